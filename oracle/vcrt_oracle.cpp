@@ -1,0 +1,408 @@
+// SPDX-License-Identifier: WTFPL
+//
+// TEST INFRASTRUCTURE — NOT PRODUCT CODE.
+// CPU restatement of the reference's per-pixel path-tracing loop, used only as the parity
+// checker by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+// legs.  Nothing under vulkancomputeraytracing_b200/ links, loads or calls this file.
+//
+// Parity status: PINNED.  In HASH mode this file is checked bit-for-bit against the
+// reference's own shader sources compiled as C++ (oracle/build_ref.py -> oracle/_ref/) and
+// against golden images produced by that build (tests/golden/, tests/test_oracle_*.py).
+//
+// Every function cites the reference lines it restates (paths relative to the reference
+// root).  Arithmetic is IEEE binary32, one rounding per written operation: build with
+// -ffp-contract=off for the bit-stable variant.  Run-time inputs replace the reference's
+// compile-time constants (shaders/include/globals.glsl:9-26 and the baked world[] table).
+//
+// Bug ledger policy: B1 B3 B4 B4b B5 B8 are MATCHED; B6 (pow of a
+// negative base) uses C powf; B7 (ray_color falls off its end) returns black; B9 every pixel
+// is rendered; B12 binary32 everywhere; B2 (the sin-hash "RNG") is kept in rng mode HASH and
+// replaced by Philox4x32-10 at the same draw sites in rng mode PHILOX.
+
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <omp.h>
+
+namespace {
+
+struct V3 { float x, y, z; };
+inline V3 v3(float x, float y, float z) { return V3{x, y, z}; }
+inline V3 add(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+inline V3 sub(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline V3 mul(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
+inline V3 scale(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }   // vec * float
+inline V3 lscale(float s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }  // float * vec
+inline V3 divs(V3 a, float s) { return v3(a.x / s, a.y / s, a.z / s); }
+inline V3 neg(V3 a) { return v3(-a.x, -a.y, -a.z); }
+inline float dot3(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline float len3(V3 a) { return std::sqrt(dot3(a, a)); }
+inline V3 unit(V3 a) { return divs(a, len3(a)); }  // GLSL normalize: v / length(v)
+inline V3 cross3(V3 a, V3 b) { return v3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
+inline V3 reflect3(V3 i, V3 n) { return sub(i, lscale(2.0f * dot3(n, i), n)); }  // GLSL reflect: I - 2*dot(N,I)*N
+
+// structures.glsl:10-16 — 10 floats per sphere, in the order the C ABI carries them.
+struct Sphere { V3 center; float radius; V3 colour; V3 texture; };
+// structures.glsl:23-30
+struct Hit { V3 point, normal; float min_t, max_t; V3 texture, colour; };
+struct Ray { V3 origin, direction; };
+
+enum { RNG_HASH = 0, RNG_PHILOX = 1 };
+
+// ---------------------------------------------------------------- Philox4x32-10
+// Salmon et al., "Parallel random numbers: as easy as 1, 2, 3" (SC'11); constants and
+// round structure of Random123's philox4x32 with 10 rounds.
+inline void philox4x32_10(const uint32_t ctr_in[4], const uint32_t key_in[2], uint32_t out[4]) {
+    uint32_t c0 = ctr_in[0], c1 = ctr_in[1], c2 = ctr_in[2], c3 = ctr_in[3];
+    uint32_t k0 = key_in[0], k1 = key_in[1];
+    for (int round = 0; round < 10; round++) {
+        uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t)p1;
+        uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+inline float u01(uint32_t bits) { return (float)(bits >> 8) * 5.9604644775390625e-08f; }  // [0,1), 24 bits
+
+// Per-path random source.  Draw sites are exactly the reference's rand() call sites:
+//   block 0           : the two pixel-jitter draws of shader.comp:48
+//   block k (k >= 1)  : the draws of the k-th scatter event (3 for lambertian/metal via
+//                       random_in_unit_sphere, functions.glsl:42-44; 1 for glass, textures.glsl:51)
+// Philox counter = (pixel index y*W+x, global sample index, block, 0), key = 64-bit seed.
+struct Rng {
+    int mode; uint32_t key[2]; uint32_t pixel, sample;
+    void block(uint32_t k, float u[4]) const {
+        uint32_t ctr[4] = {pixel, sample, k, 0u}, r[4];
+        philox4x32_10(ctr, key, r);
+        for (int i = 0; i < 4; i++) u[i] = u01(r[i]);
+    }
+};
+
+// functions.glsl:10-12
+inline float hash_rand(float cx, float cy) {
+    float d = cx * 12.9898f + cy * 78.233f;
+    float s = std::sin(d) * 43758.5453f;
+    return s - std::floor(s);
+}
+
+// functions.glsl:14-40.  Returns true and updates the record when sphere s is the new nearest hit.
+inline bool hit_sphere(const Sphere& s, const Ray& r, Hit& rec) {
+    V3 oc = sub(r.origin, s.center);
+    float a = dot3(r.direction, r.direction);
+    float half_b = dot3(oc, r.direction);
+    float c = dot3(oc, oc) - s.radius * s.radius;
+    float discriminant = half_b * half_b - a * c;
+    if (discriminant < 0) return false;
+    float sqrtd = std::sqrt(discriminant);
+    float root = (-half_b - sqrtd) / a;
+    if (root <= rec.min_t || rec.max_t <= root) {
+        root = (-half_b + sqrtd) / a;
+        if (root <= rec.min_t || rec.max_t <= root) return false;
+    }
+    rec.max_t = root;
+    rec.point = add(lscale(root, r.direction), r.origin);
+    rec.normal = divs(sub(rec.point, s.center), s.radius);  // outward, never face-forwarded
+    rec.texture = s.texture;
+    rec.colour = s.colour;
+    return true;
+}
+
+// functions.glsl:42-44 (bug B4: a unit vector in the positive octant).  u = the three draws.
+inline V3 random_in_unit_sphere(const Rng& rng, V3 seed, const float u[4]) {
+    if (rng.mode == RNG_HASH)
+        return unit(v3(hash_rand(seed.x, seed.y), hash_rand(seed.x, seed.z), hash_rand(seed.y, seed.z)));
+    return unit(v3(u[0], u[1], u[2]));
+}
+
+// functions.glsl:46-56
+inline bool modified_refract(V3 v, V3 n, float ni_over_nt, V3& refracted) {
+    float dt = dot3(v, n);
+    float discriminant = 1.f - ni_over_nt * ni_over_nt * (1.f - dt * dt);
+    if (discriminant > 0.f) {
+        refracted = sub(lscale(ni_over_nt, sub(v, scale(n, dt))), scale(n, std::sqrt(discriminant)));
+        return true;
+    }
+    return false;
+}
+
+// functions.glsl:58-62 (bug B6: pow of a negative base -> C powf)
+inline float schlick(float cosine, float ior) {
+    float r0 = (1.f - ior) / (1.f + ior);
+    r0 = r0 * r0;
+    return r0 + (1.f - r0) * std::pow(1.f - cosine, 5.f);
+}
+
+// textures.glsl:19-25
+inline void texture_lambertian(const Hit& rec, V3& colour, Ray& ray, const Rng& rng, const float u[4]) {
+    V3 direction = add(rec.normal, random_in_unit_sphere(rng, ray.direction, u));
+    colour = scale(mul(colour, rec.colour), rec.texture.y);  // bug B4b: extra * texture.y
+    ray.origin = rec.point;
+    ray.direction = direction;
+}
+
+// textures.glsl:27-56
+inline void texture_glass(const Hit& rec, V3& /*colour*/, Ray& ray, const Rng& rng, const float u[4]) {
+    V3 outward_normal, refracted = v3(0, 0, 0);
+    V3 reflected = reflect3(ray.direction, rec.normal);
+    float ni_over_nt, reflect_prob, cosine;
+    if (dot3(ray.direction, rec.normal) > 0.f) {
+        outward_normal = neg(rec.normal);
+        ni_over_nt = rec.texture.y;
+        cosine = dot3(ray.direction, rec.normal);
+        cosine = std::sqrt(1.f - rec.texture.y * rec.texture.y * (1.f - cosine * cosine));
+    } else {
+        outward_normal = rec.normal;
+        ni_over_nt = 1.f / rec.texture.y;
+        cosine = -dot3(ray.direction, rec.normal);
+    }
+    if (modified_refract(ray.direction, outward_normal, ni_over_nt, refracted))
+        reflect_prob = schlick(cosine, rec.texture.y);
+    else
+        reflect_prob = 1.f;
+    ray.origin = rec.point;
+    float pick = (rng.mode == RNG_HASH) ? hash_rand(rec.point.x, rec.point.y) : u[0];
+    if (pick < reflect_prob) ray.direction = reflected;
+    else ray.direction = refracted;
+}
+
+// textures.glsl:58-63
+inline void texture_metal(const Hit& rec, V3& colour, Ray& ray, const Rng& rng, const float u[4]) {
+    V3 direction = add(reflect3(ray.direction, rec.normal),
+                       lscale(rec.texture.y, random_in_unit_sphere(rng, ray.direction, u)));
+    colour = mul(colour, rec.colour);
+    ray.origin = rec.point;
+    ray.direction = direction;
+}
+
+struct Stats { uint64_t rays, exhausted, hits[4], path_hist[8]; };
+
+// functions.glsl:65-92 + textures.glsl:65-71
+inline V3 ray_color(Ray r, const Sphere* world, int count, int max_depth, const Rng& rng, Stats& st) {
+    Hit rec; rec.max_t = 0; rec.min_t = 0;
+    V3 color = v3(1.f, 1.f, 1.f);
+    for (int pass = 0; pass < max_depth; pass++) {
+        st.rays++;
+        bool t = false;
+        rec.max_t = 1e5f;  // globals.glsl:26 `infinity`
+        rec.min_t = 0.001f;
+        for (int i = 0; i < count; i++)
+            if (hit_sphere(world[i], r, rec)) t = true;
+        if (t) {
+            float u[4] = {0, 0, 0, 0};
+            if (rng.mode == RNG_PHILOX) rng.block((uint32_t)pass + 1u, u);
+            int kind = (int)rec.texture.x;
+            if (kind >= 1 && kind <= 3) st.hits[kind]++; else st.hits[0]++;
+            switch (kind) {  // textures.glsl:65-71; any other id leaves the ray unchanged (B13)
+                case 1: texture_lambertian(rec, color, r, rng, u); break;
+                case 2: texture_metal(rec, color, r, rng, u); break;
+                case 3: texture_glass(rec, color, r, rng, u); break;
+            }
+        } else {  // sky
+            V3 unit_direction = unit(r.direction);
+            float a = 0.5f * (unit_direction.y + 1.0f);
+            V3 sky = add(scale(v3(1.f, 1.f, 1.f), 1.0f - a), scale(v3(.5f, .7f, 1.f), a));  // GLSL mix
+            st.path_hist[pass < 7 ? pass : 7]++;
+            return mul(color, sky);
+        }
+    }
+    st.exhausted++;  // bug B7: defined as black
+    return v3(0.f, 0.f, 0.f);
+}
+
+// shader.comp:18-39.  Camera floats: lookfrom[3], lookat[3], vup[3], vfov (globals.glsl:21-24).
+struct Frame { V3 center, pixel00, du, dv; };
+inline Frame make_frame(const float* cam, int width, int height) {
+    V3 lookfrom = v3(cam[0], cam[1], cam[2]), lookat = v3(cam[3], cam[4], cam[5]), vup = v3(cam[6], cam[7], cam[8]);
+    float vfov = cam[9];
+    float focal_length = len3(sub(lookfrom, lookat));
+    float theta = vfov * 0.017453292519943295f;  // radians()
+    float h = std::tan(theta / 2);
+    float viewport_height = 2 * h * focal_length;
+    float viewport_width = viewport_height * (float)(width / height);  // bug B1: integer division
+    V3 w = unit(sub(lookfrom, lookat));
+    V3 u = unit(cross3(vup, w));
+    V3 v = cross3(w, u);
+    V3 viewport_u = lscale(viewport_width, u);
+    V3 viewport_v = lscale(viewport_height, neg(v));
+    Frame f;
+    f.du = divs(viewport_u, (float)height);  // bug B1: both deltas divide by the HEIGHT
+    f.dv = divs(viewport_v, (float)height);
+    V3 upper_left = sub(sub(sub(lookfrom, lscale(focal_length, w)), divs(viewport_u, 2.f)), divs(viewport_v, 2.f));
+    f.pixel00 = add(upper_left, lscale(0.5f, add(f.du, f.dv)));
+    f.center = lookfrom;
+    return f;
+}
+
+// shader.comp:42-57 for one pixel; sample indices [sample_offset, sample_offset + spp).
+// Returns the SUM over the samples (the caller divides, so sharded renders can be added).
+inline V3 pixel_sum(const Frame& f, int px, int py, int width, const Sphere* world, int count, int spp,
+                    int sample_offset, int max_depth, int rng_mode, uint64_t seed, Stats& st) {
+    V3 pixel_center = add(add(f.pixel00, lscale((float)px, f.du)), lscale((float)py, f.dv));
+    V3 sum = v3(0.f, 0.f, 0.f);
+    Rng rng; rng.mode = rng_mode; rng.key[0] = (uint32_t)seed; rng.key[1] = (uint32_t)(seed >> 32);
+    rng.pixel = (uint32_t)(py * width + px);
+    for (int s = 0; s < spp; s++) {
+        int i = sample_offset + s;
+        rng.sample = (uint32_t)i;
+        float ju, jv;
+        if (rng_mode == RNG_HASH) { ju = hash_rand((float)i, (float)i); jv = hash_rand((float)(i + 1), (float)(i + 1)); }
+        else { float u[4]; rng.block(0u, u); ju = u[0]; jv = u[1]; }
+        V3 random_square = add(lscale(-0.5f + ju, f.du), lscale(-0.5f + jv, f.dv));
+        V3 pixel_sample = add(pixel_center, random_square);
+        Ray r; r.origin = f.center; r.direction = sub(pixel_sample, f.center);  // never normalised (B3)
+        sum = add(sum, ray_color(r, world, count, max_depth, rng, st));
+    }
+    return sum;
+}
+
+}  // namespace
+
+extern "C" {
+
+// spheres: count x 10 floats (centre xyz, radius, colour rgb, texture xyz); camera: 10 floats.
+// rgba: width*height*4 floats; receives sum/spp_total when normalise != 0, else the raw sum
+// (alpha = 1 either way, shader.comp:44).  stats (may be NULL): [0] rays, [1] depth-exhausted
+// samples, [2..5] hits by texture id 0(other)/1/2/3, [6..13] paths that reached the sky after
+// 1,2,...,7, >=8 rays.
+int oracle_render(const float* spheres, int count, const float* camera, int width, int height, int spp,
+                  int sample_offset, int max_depth, int rng_mode, uint64_t seed, int normalise, int threads,
+                  float* rgba, uint64_t* stats) {
+    if (!spheres || !camera || !rgba || count < 0 || width <= 0 || height <= 0 || spp <= 0 || max_depth < 0) return -1;
+    const Sphere* world = reinterpret_cast<const Sphere*>(spheres);
+    Frame f = make_frame(camera, width, height);
+    Stats total; std::memset(&total, 0, sizeof(total));
+    if (threads > 0) omp_set_num_threads(threads);
+#pragma omp parallel
+    {
+        Stats st; std::memset(&st, 0, sizeof(st));
+#pragma omp for schedule(dynamic, 1) nowait
+        for (int y = 0; y < height; y++) {
+            for (int x = 0; x < width; x++) {
+                V3 sum = pixel_sum(f, x, y, width, world, count, spp, sample_offset, max_depth, rng_mode, seed, st);
+                if (normalise) sum = divs(sum, (float)spp);
+                float* px = rgba + 4 * ((size_t)y * width + x);
+                px[0] = sum.x; px[1] = sum.y; px[2] = sum.z; px[3] = 1.0f;
+            }
+        }
+#pragma omp critical
+        {
+            total.rays += st.rays; total.exhausted += st.exhausted;
+            for (int i = 0; i < 4; i++) total.hits[i] += st.hits[i];
+            for (int i = 0; i < 8; i++) total.path_hist[i] += st.path_hist[i];
+        }
+    }
+    if (stats) {
+        stats[0] = total.rays; stats[1] = total.exhausted;
+        for (int i = 0; i < 4; i++) stats[2 + i] = total.hits[i];
+        for (int i = 0; i < 8; i++) stats[6 + i] = total.path_hist[i];
+    }
+    return 0;
+}
+
+// Known-answer entry points (tests/test_oracle_kat.py).
+float oracle_hash_rand(float x, float y) { return hash_rand(x, y); }
+float oracle_schlick(float cosine, float ior) { return schlick(cosine, ior); }
+int oracle_refract(const float* v, const float* n, float eta, float* out) {
+    V3 r = v3(0, 0, 0);
+    bool ok = modified_refract(v3(v[0], v[1], v[2]), v3(n[0], n[1], n[2]), eta, r);
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
+    return ok ? 1 : 0;
+}
+void oracle_philox(const uint32_t* ctr, const uint32_t* key, uint32_t* out) { philox4x32_10(ctr, key, out); }
+// out: focal, h, viewport_h, then w? no — 12 floats: center, pixel00, du, dv.
+void oracle_camera(const float* camera, int width, int height, float* out) {
+    Frame f = make_frame(camera, width, height);
+    const V3 v[4] = {f.center, f.pixel00, f.du, f.dv};
+    for (int i = 0; i < 4; i++) { out[3 * i] = v[i].x; out[3 * i + 1] = v[i].y; out[3 * i + 2] = v[i].z; }
+}
+// Nearest hit of one ray; returns the sphere index (first index wins exact ties) or -1.
+int oracle_first_hit(const float* spheres, int count, const float* origin, const float* direction, float* t) {
+    const Sphere* world = reinterpret_cast<const Sphere*>(spheres);
+    Ray r; r.origin = v3(origin[0], origin[1], origin[2]); r.direction = v3(direction[0], direction[1], direction[2]);
+    Hit rec; rec.min_t = 0.001f; rec.max_t = 1e5f; int best = -1;
+    for (int i = 0; i < count; i++) if (hit_sphere(world[i], r, rec)) best = i;
+    if (t) *t = rec.max_t;
+    return best;
+}
+
+// ------------------------------------------------------------------ scene producer
+// SceneGenerator.cpp:23-56 restated as a function that fills sphere records instead of
+// printing GLSL text.  libstdc++'s default-seeded std::mt19937 (5489) feeding
+// uniform_real_distribution<double>(0,1) is restated as MT19937 + generate_canonical<double,53>
+// (two 32-bit draws per double: (lo + hi*2^32) / 2^64).  The reference leaves the evaluation
+// order of its random_double() ARGUMENTS unspecified; g++ on x86-64 evaluates them right to
+// left, which is what reproduces the table baked into globals.glsl:31-515, so that order is
+// written out explicitly here.  Values pass through "%.2f" exactly as the printed text does.
+namespace {
+struct MT19937 {
+    uint32_t mt[624]; int idx;
+    explicit MT19937(uint32_t seed = 5489u) {
+        mt[0] = seed;
+        for (int i = 1; i < 624; i++) mt[i] = 1812433253u * (mt[i - 1] ^ (mt[i - 1] >> 30)) + (uint32_t)i;
+        idx = 624;
+    }
+    uint32_t next() {
+        if (idx >= 624) {
+            for (int i = 0; i < 624; i++) {
+                uint32_t y = (mt[i] & 0x80000000u) | (mt[(i + 1) % 624] & 0x7fffffffu);
+                mt[i] = mt[(i + 397) % 624] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+            }
+            idx = 0;
+        }
+        uint32_t y = mt[idx++];
+        y ^= y >> 11; y ^= (y << 7) & 0x9d2c5680u; y ^= (y << 15) & 0xefc60000u; y ^= y >> 18;
+        return y;
+    }
+    double canonical() {
+        double lo = (double)next(), hi = (double)next();
+        double r = (lo + hi * 4294967296.0) / 18446744073709551616.0;
+        return r >= 1.0 ? std::nextafter(1.0, 0.0) : r;
+    }
+};
+inline float round2(double v) {  // the "%.2f" text round trip, then GLSL's binary32 literal
+    char buf[64]; std::snprintf(buf, sizeof buf, "%.2f", v);
+    return std::strtof(buf, nullptr);
+}
+}  // namespace
+// grid_half = 11 reproduces the reference scene.  lambert_below / metal_below are the
+// choose_mat thresholds (0.8 / 0.95 in the reference).  Appends the three radius-1 spheres
+// (SceneGenerator.cpp:50-55) and then the hand-added ground sphere (globals.glsl:517) LAST.
+// Returns the number of spheres written, or -1 if capacity is too small.
+int oracle_generate_scene(int grid_half, double lambert_below, double metal_below, float* out, int capacity) {
+    MT19937 gen;
+    int n = 0;
+    auto put = [&](float cx, float cy, float cz, float r, float cr, float cg, float cb, float kind, float param) -> bool {
+        if (n >= capacity) return false;
+        float* o = out + 10 * n++;
+        o[0] = cx; o[1] = cy; o[2] = cz; o[3] = r; o[4] = cr; o[5] = cg; o[6] = cb; o[7] = kind; o[8] = param; o[9] = 0.0f;
+        return true;
+    };
+    for (int a = -grid_half; a < grid_half; a++) {
+        for (int b = -grid_half; b < grid_half; b++) {
+            double choose_mat = gen.canonical();
+            double rz = gen.canonical();  // right-to-left: the z argument draws first
+            double rx = gen.canonical();
+            float cx = (float)(a + 0.9 * rx), cy = (float)0.2, cz = (float)(b + 0.9 * rz);
+            float dx = cx - 4.f, dy = cy - 0.2f, dz = cz - 0.f;
+            if (dx * dx + dy * dy + dz * dz < 0.9) continue;  // squared length vs 0.9 (B13)
+            float px = round2(cx), py = round2(cy), pz = round2(cz);
+            if (choose_mat < lambert_below || choose_mat < metal_below) {
+                double p4 = gen.canonical(), p3 = gen.canonical(), p2 = gen.canonical(), p1 = gen.canonical();
+                float kind = choose_mat < lambert_below ? 1.f : 2.f;
+                if (!put(px, py, pz, 0.2f, round2(p1), round2(p2), round2(p3), kind, round2(p4))) return -1;
+            } else {
+                if (!put(px, py, pz, 0.2f, 1.0f, 1.0f, 1.0f, 3.f, 1.5f)) return -1;
+            }
+        }
+    }
+    if (!put(0, 1, 0, 1.0f, 1.0f, 1.0f, 1.0f, 3.f, 1.5f)) return -1;
+    if (!put(-4, 1, 0, 1.0f, 0.4f, 0.2f, 0.1f, 1.f, 1.0f)) return -1;
+    if (!put(4, 1, 0, 1.0f, 0.7f, 0.6f, 0.5f, 2.f, 1.0f)) return -1;
+    if (!put(0, -1000, 0, 1000.f, 0.5f, 0.5f, 0.5f, 1.f, 1.0f)) return -1;
+    return n;
+}
+}

@@ -1,0 +1,170 @@
+/* @file vcrt.h
+
+    C ABI of the B200 path-tracing layer: the boundary that replaces the Vulkan compute
+    dispatch of the reference (Renderer.cpp:204-225 record, :678-686 submit) and its
+    SPIR-V loader (Shader.cpp:34-95).  Plain pointers and sizes only; no CUDA, torch or
+    C++ types cross this boundary, so cgo / JNI / ctypes / a C++ host can all bind it.
+    SPDX-License-Identifier: WTFPL
+
+    Error convention (reference: VkResult returned to main, VulkanComputeRayTracing.cpp:20-35):
+    every entry point returns 0 (VCRT_SUCCESS, same value as VK_SUCCESS) or a negative code;
+    nothing throws, nothing logs.  cudaGetLastErrorString() gives the text of the last failure.
+    The layer is single-threaded and not re-entrant, like the reference renderer (global state,
+    Renderer.cpp:13-33).  There is NO CPU fallback: without a usable CUDA device every
+    compute entry point fails with VCRT_ERROR_NO_DEVICE.
+*/
+#ifndef VCRT_H
+#define VCRT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifndef IN
+#define IN  /* reference include/Common.hpp:11-12 */
+#define OUT
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    VCRT_SUCCESS = 0,
+    VCRT_ERROR_INVALID_ARGUMENT = -1,
+    VCRT_ERROR_NO_DEVICE = -2,       /* no CUDA device / driver: there is no CPU path */
+    VCRT_ERROR_NOT_READY = -3,       /* cudaRender before cudaUploadScene, download before render */
+    VCRT_ERROR_OUT_OF_MEMORY = -4,
+    VCRT_ERROR_CUDA = -5,            /* sticky CUDA error, see cudaGetLastErrorString */
+    VCRT_ERROR_NCCL = -6,
+    VCRT_ERROR_UNSUPPORTED = -7,
+    VCRT_ERROR_SCENE = -8            /* kernel met a texture id outside 1..3 (reference: silent no-op, B13) */
+};
+
+/* One sphere, field for field the GLSL struct (shaders/include/structures.glsl:10-16).
+   texture[0] = material id stored as a float: 1 lambertian, 2 metal, 3 glass
+   (shaders/include/textures.glsl:10-12); texture[1] = reflect ratio / fuzz / ior;
+   texture[2] unused. 40 bytes, no padding. */
+typedef struct VcrtSphere {
+    float center[3];
+    float radius;
+    float colour[3];
+    float texture[3];
+} VcrtSphere;
+
+/* Camera constants of shaders/include/globals.glsl:21-24. */
+typedef struct VcrtCamera {
+    float lookfrom[3];
+    float lookat[3];
+    float vup[3];
+    float vfov;  /* degrees */
+} VcrtCamera;
+
+/* How rays find their nearest sphere. */
+enum {
+    VCRT_TRAVERSAL_AUTO = 0,    /* brute force while the scene fits shared memory, else LBVH */
+    VCRT_TRAVERSAL_BRUTE = 1,   /* every ray tests every sphere (what the reference does, functions.glsl:77-81) */
+    VCRT_TRAVERSAL_LBVH = 2,    /* GPU-built linear BVH */
+    VCRT_TRAVERSAL_SIMPLE = 3   /* one thread per pixel, reference statement order; the on-device cross-check */
+};
+
+enum {
+    VCRT_FLAG_ACCUMULATE = 1u << 0,   /* add this call's samples to the sums already held (progressive frames) */
+    VCRT_FLAG_NO_REDUCE = 1u << 1,    /* multi-GPU: skip the NCCL reduce, keep the local partial sums */
+    VCRT_FLAG_ALL_REDUCE = 1u << 2,   /* multi-GPU: every rank ends up with the full image, not just rank 0 */
+    VCRT_FLAG_COUNT_STATS = 1u << 3   /* also fill the per-material / path-length counters (slower) */
+};
+
+/* Run-time stand-ins for the shader's compile-time constants (globals.glsl:9-17).
+   Zero-initialise, then set what you need; vcrtDefaultRenderParams() gives the reference's
+   values (1280x720, 1 spp, depth 50). */
+typedef struct VcrtRenderParams {
+    uint32_t width;            /* IMAGE_WIDTH */
+    uint32_t height;           /* IMAGE_HEIGHT */
+    uint32_t samplesPerPixel;  /* SAMPLES_PER_PIXEL rendered by THIS call on THIS device */
+    uint32_t maxDepth;         /* MAX_RECURSION_LEVEL */
+    uint64_t seed;             /* Philox key */
+    uint32_t sampleOffset;     /* global index of this call's first sample (spp sharding / progressive) */
+    uint32_t totalSamples;     /* divisor of the final image; 0 = samples accumulated so far (after reduce: over all ranks) */
+    uint32_t traversal;        /* VCRT_TRAVERSAL_* */
+    uint32_t flags;            /* VCRT_FLAG_* */
+    uint32_t sampleChunks;     /* 0 = auto; 1 = a pixel's samples are summed strictly in index order */
+    uint32_t reserved[3];
+} VcrtRenderParams;
+
+/* Counters of the last cudaRender on this device. */
+typedef struct VcrtRenderStats {
+    uint64_t samples;          /* pixel-samples traced */
+    uint64_t rays;             /* path segments traced (one per pass of functions.glsl:73) */
+    uint64_t sphereTests;      /* brute force: rays * sphere count; LBVH: leaf sphere tests actually made */
+    uint64_t nodeVisits;       /* LBVH only */
+    uint64_t depthExhausted;   /* samples that hit maxDepth (bug B7, counted as black) */
+    uint64_t badMaterial;      /* hits on a texture id outside 1..3 */
+    uint64_t candidates;       /* brute force: tests that survived the conservative filter */
+    uint64_t listOverflows;    /* brute force: rays that fell back to the exhaustive exact scan */
+    uint64_t hitsByMaterial[4];/* VCRT_FLAG_COUNT_STATS: [0] other, [1] lambertian, [2] metal, [3] glass */
+    uint64_t pathLength[8];    /* VCRT_FLAG_COUNT_STATS: paths ending in the sky after 1..7, >=8 rays */
+    float renderKernelMs;      /* CUDA-event time of the path-tracing kernel(s) alone */
+    float totalMs;             /* whole cudaRender: kernels + combine + reduce + normalise */
+    uint32_t kernelLaunches;   /* kernels this call launched */
+    uint32_t traversalUsed;    /* VCRT_TRAVERSAL_* actually run */
+    uint32_t sampleChunksUsed;
+    uint32_t reserved;
+} VcrtRenderStats;
+
+void vcrtDefaultRenderParams(OUT VcrtRenderParams* params);
+void vcrtDefaultCamera(OUT VcrtCamera* camera);
+
+/* Replaces: the baked `const sphere world[]` + camera globals (globals.glsl:21-24, :29-518) that
+   the reference compiles into the shader, and vkCreateShaderModule of that shader
+   (Shader.cpp:34-95, Renderer.cpp:240, :534-543).  Copies the host AoS, builds the device SoA
+   (and the LBVH when asked for / needed).  The caller keeps ownership of `spheres`. */
+int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, IN const VcrtCamera* camera);
+
+/* Replaces: recordComputeCommandBuffer + vkQueueSubmit + the device wait that follows a frame
+   (Renderer.cpp:204-225, :678-686; platform/Linux.cpp:365).  Synchronous: returns when the
+   normalised RGBA32F image (the reference's storage image, Renderer.cpp:433-453) is complete in
+   device memory owned by the layer. */
+int cudaRender(IN const VcrtRenderParams* params);
+
+/* Replaces: the fragment stage's texelFetch of the result image (shaders/shader.frag:11-14).
+   Copies width*height*4 floats (linear radiance, alpha = 1; no gamma, bug B8). */
+int cudaDownloadImage(OUT float* rgba, IN size_t bytes);
+
+/* Raw per-pixel SUMS (not divided) of this device, for callers that reduce themselves. */
+int cudaDownloadSums(OUT float* rgba, IN size_t bytes);
+
+/* Replaces: EndRenderingOperation's destruction of the image, memory, pipeline
+   (Renderer.cpp:737-739, :752-763, :770-772).  Tolerates never-created state. */
+int cudaDestroyRenderer(void);
+
+/* CUDA analogue of picking the physical device (Environment.cpp:157-165). Default: device 0. */
+int cudaSelectDevice(IN int device);
+
+int cudaGetRenderStats(OUT VcrtRenderStats* stats);
+const char* cudaGetLastErrorString(void);
+
+/* Device pointer + size of the layer-owned result image / sum buffer, for zero-copy consumers
+   in the same process (e.g. a torch tensor view). */
+int cudaGetDeviceImage(OUT void** devicePointer, OUT size_t* bytes);
+int cudaGetDeviceSums(OUT void** devicePointer, OUT size_t* bytes);
+
+/* ---- multi-GPU: samples-per-pixel sharded over ranks, one NCCL reduce of the float sums ---- */
+/* One process per GPU: rank 0 calls cudaCommGetUniqueId, ships the 128 bytes to every rank by
+   any means (the Python host uses torch.distributed), every rank calls cudaCommInitRank. */
+int cudaCommGetUniqueId(OUT void* id128);
+int cudaCommInitRank(IN const void* id128, IN int rank, IN int worldSize);
+int cudaCommDestroy(void);
+/* Max over ranks of one float (timing), through the same communicator. */
+int cudaCommMaxFloat(IN float value, OUT float* maxValue);
+int cudaCommBarrier(void);
+
+/* ---- measurement ---- */
+/* Runs an FFMA-only kernel on the selected device and reports the FP32 FMA rate it reached:
+   the denominator of the roofline (MEASURED_PEAKS.json carries HBM and bf16 only). */
+int cudaMeasureFp32Peak(OUT double* tflops, OUT double* smClockMHz);
+int cudaGetDeviceInfo(OUT int* smCount, OUT int* maxClockKHz, OUT char* name, IN size_t nameBytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VCRT_H */

@@ -1,0 +1,591 @@
+/* @file vcrt_cabi.cu
+
+    The C ABI of include/vcrt.h: scene upload (AoS -> device SoA blob), render dispatch,
+    partial-sum combine, the NCCL reduce of the float sums, normalisation and read-back.
+    Host code is C++ in the reference's C flavour: free functions, file-static state,
+    integer return codes, no exceptions (reference Renderer.cpp:13-33, README.md:7).
+    SPDX-License-Identifier: WTFPL
+*/
+#include "../../include/vcrt.h"
+#include "vcrt_kernel_simple.cuh"
+#include "vcrt_kernel_scan.cuh"
+
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+using namespace vcrt;
+
+// ------------------------------------------------------------------ file-static state
+// (reference Renderer.cpp:13-33 keeps its pipeline, image and memory handles the same way)
+static int cudaComputeDevice = 0;
+static bool cudaComputeDeviceReady = false;
+static int cudaComputeSmCount = 0;
+static cudaStream_t cudaComputeStream = nullptr;
+static cudaEvent_t cudaComputeEvents[4] = {nullptr, nullptr, nullptr, nullptr};
+
+static unsigned char* cudaComputeSceneBlob = nullptr;   // device copy of the SoA blob
+static SceneBlob cudaComputeSceneHeader;
+static bool cudaComputeSceneReady = false;
+static VcrtCamera cudaComputeCamera;
+
+static float4* cudaComputeSumPlanes = nullptr;          // [chunks][W*H] partial sums of the last render
+static size_t cudaComputeSumPlanesBytes = 0;
+static float4* cudaComputeAccumulated = nullptr;        // [W*H] sums over all samples so far (this device)
+static float4* cudaComputeReduced = nullptr;            // [W*H] sums after the cross-device reduce
+static long long* cudaComputeFixedSums = nullptr;       // [W*H][4] signed 32.32 fixed-point sums (order-independent accumulation)
+static long long* cudaComputeFixedReduced = nullptr;    // the same after the cross-device reduce
+static bool cudaComputeAccumulatedIsFixed = false;
+static float4* cudaComputeResultImage = nullptr;        // [W*H] normalised RGBA32F (reference Renderer.cpp:433-453)
+static uint32_t cudaComputeImageWidth = 0, cudaComputeImageHeight = 0;
+static uint64_t cudaComputeAccumulatedSamples = 0;
+static bool cudaComputeImageValid = false;
+static unsigned long long* cudaComputeCounters = nullptr;
+static unsigned int* cudaComputeWorkCounter = nullptr;
+static VcrtRenderStats cudaComputeLastStats;
+static char cudaComputeLastError[512] = "";
+
+static int fail(int code, const char* fmt, const char* detail) {
+    snprintf(cudaComputeLastError, sizeof cudaComputeLastError, fmt, detail ? detail : "");
+    return code;
+}
+#define CUDA_TRY(expr)                                                                    \
+    do {                                                                                  \
+        cudaError_t cudaTryResult = (expr);                                               \
+        if (cudaTryResult != cudaSuccess)                                                 \
+            return fail(cudaTryResult == cudaErrorMemoryAllocation ? VCRT_ERROR_OUT_OF_MEMORY : VCRT_ERROR_CUDA, \
+                        #expr ": %s", cudaGetErrorString(cudaTryResult));                 \
+    } while (0)
+
+static int ensureDevice(void) {
+    if (cudaComputeDeviceReady) return VCRT_SUCCESS;
+    int deviceCount = 0;
+    cudaError_t e = cudaGetDeviceCount(&deviceCount);
+    if (e != cudaSuccess || deviceCount == 0)
+        return fail(VCRT_ERROR_NO_DEVICE, "no CUDA device available (%s); this library has no CPU path", cudaGetErrorString(e));
+    if (cudaComputeDevice >= deviceCount) return fail(VCRT_ERROR_INVALID_ARGUMENT, "device index out of range%s", "");
+    CUDA_TRY(cudaSetDevice(cudaComputeDevice));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, cudaComputeDevice));
+    if (prop.major < 10) return fail(VCRT_ERROR_UNSUPPORTED, "device is not sm_100 class (%s)", prop.name);
+    cudaComputeSmCount = prop.multiProcessorCount;
+    CUDA_TRY(cudaStreamCreateWithFlags(&cudaComputeStream, cudaStreamNonBlocking));
+    for (int i = 0; i < 4; i++) CUDA_TRY(cudaEventCreate(&cudaComputeEvents[i]));
+    CUDA_TRY(cudaMalloc(&cudaComputeCounters, sizeof(unsigned long long) * CTR_COUNT));
+    CUDA_TRY(cudaMalloc(&cudaComputeWorkCounter, sizeof(unsigned int)));
+    cudaComputeDeviceReady = true;
+    return VCRT_SUCCESS;
+}
+
+extern "C" const char* cudaGetLastErrorString(void) { return cudaComputeLastError; }
+
+extern "C" void vcrtDefaultRenderParams(OUT VcrtRenderParams* params) {
+    if (!params) return;
+    memset(params, 0, sizeof *params);
+    params->width = 1280; params->height = 720;   // globals.glsl:16-17, Common.hpp:23-24
+    params->samplesPerPixel = 1;                   // globals.glsl:12
+    params->maxDepth = 50;                         // globals.glsl:14
+    params->traversal = VCRT_TRAVERSAL_AUTO;
+}
+
+extern "C" void vcrtDefaultCamera(OUT VcrtCamera* camera) {
+    if (!camera) return;
+    const VcrtCamera c = {{13.f, 2.f, 3.f}, {0.f, 0.f, 0.f}, {0.f, 1.f, 0.f}, 20.f};  // globals.glsl:21-24
+    *camera = c;
+}
+
+extern "C" int cudaSelectDevice(IN int device) {
+    if (device < 0) return fail(VCRT_ERROR_INVALID_ARGUMENT, "negative device index%s", "");
+    if (cudaComputeDeviceReady && device != cudaComputeDevice)
+        return fail(VCRT_ERROR_NOT_READY, "cudaSelectDevice after the renderer was created; call cudaDestroyRenderer first%s", "");
+    cudaComputeDevice = device;
+    return ensureDevice();
+}
+
+extern "C" int cudaGetDeviceInfo(OUT int* smCount, OUT int* maxClockKHz, OUT char* name, IN size_t nameBytes) {
+    int rc = ensureDevice();
+    if (rc) return rc;
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, cudaComputeDevice));
+    if (smCount) *smCount = prop.multiProcessorCount;
+    if (maxClockKHz) CUDA_TRY(cudaDeviceGetAttribute(maxClockKHz, cudaDevAttrClockRate, cudaComputeDevice));
+    if (name && nameBytes) { strncpy(name, prop.name, nameBytes - 1); name[nameBytes - 1] = 0; }
+    return VCRT_SUCCESS;
+}
+
+// ------------------------------------------------------------------ scene upload
+// Filter margin (see vcrt_kernel_scan.cuh).  The scan passes sphere (c, r) for ray (o, d) when
+//     fl( ((c-o).u)^2 + ((c-o).v)^2 - R2 ) <= kappa*|o|^2,     R2 = r^2 + kappa*(|c|^2 + r^2)
+// and the exact test (hit_exact, the reference's arithmetic) can only succeed when its own
+// computed discriminant is >= 0.  Both computations differ from the real-number quantity
+// a*(r^2 - D^2) (D = distance from c to the ray's line) by rounding error:
+//   reference side: <= ~18 eps * (|oc|^2 + r^2)      (oc rounding, two dot products, a*c)
+//   filter side   : <= ~30 eps * (|o| + |c|)^2       (basis orthonormality ~4 eps, the expanded
+//                                                     form c.u - o.u, the two squares)
+// with eps = 2^-24 and |oc|^2 <= 2(|o|^2+|c|^2), (|o|+|c|)^2 <= 2(|o|^2+|c|^2) the total is below
+// 96 eps (|o|^2 + |c|^2 + r^2) < kappa (|o|^2 + |c|^2 + r^2) for kappa = 2^-17 = 128 eps.
+// So every sphere the reference arithmetic would hit is in the candidate list; extra
+// candidates cost time, never correctness.  tests/test_gpu_parity.py checks the consequence:
+// VCRT_TRAVERSAL_BRUTE and VCRT_TRAVERSAL_SIMPLE images are bit-identical.
+static const float kAlwaysRadius = 50.0f;   // spheres this large (the ground) skip the filter: tested exactly for every ray
+static const uint32_t kMaxAlways = 64;
+
+extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, IN const VcrtCamera* camera) {
+    if ((!spheres && count) || !camera) return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaUploadScene: null argument%s", "");
+    int rc = ensureDevice();
+    if (rc) return rc;
+
+    uint32_t* order = new uint32_t[count ? count : 1];
+    uint32_t scanCount = 0, alwaysCount = 0;
+    for (uint32_t i = 0; i < count; i++) if (!(spheres[i].radius > kAlwaysRadius)) order[scanCount++] = i;
+    for (uint32_t i = 0; i < count; i++) if (spheres[i].radius > kAlwaysRadius) order[scanCount + alwaysCount++] = i;
+    if (alwaysCount > kMaxAlways) {   // too many huge spheres: keep the first kMaxAlways out, scan the rest like any other
+        scanCount = 0; alwaysCount = 0; uint32_t kept = 0;
+        for (uint32_t i = 0; i < count; i++) { bool big = spheres[i].radius > kAlwaysRadius && kept < kMaxAlways; if (big) kept++; else order[scanCount++] = i; }
+        kept = 0;
+        for (uint32_t i = 0; i < count; i++) if (spheres[i].radius > kAlwaysRadius && kept < kMaxAlways) { order[scanCount + alwaysCount++] = i; kept++; }
+    }
+    const uint32_t scanPad = (scanCount + 7u) & ~7u;   // the scan walks the list 8 spheres at a time
+
+    SceneBlob hdr; memset(&hdr, 0, sizeof hdr);
+    hdr.count = count; hdr.scanCount = scanCount; hdr.scanPad = scanPad; hdr.alwaysCount = alwaysCount;
+    hdr.offHot = (uint32_t)sizeof(SceneBlob);
+    hdr.offShape = hdr.offHot + scanPad * 16u;
+    hdr.offSurf = hdr.offShape + count * 16u;
+    hdr.offKind = hdr.offSurf + count * 16u;
+    hdr.bytes = (hdr.offKind + count * 4u + 15u) & ~15u;
+    unsigned char* host = (unsigned char*)calloc(1, hdr.bytes);
+    if (!host) { delete[] order; return fail(VCRT_ERROR_OUT_OF_MEMORY, "scene blob%s", ""); }
+    float4* hot = (float4*)(host + hdr.offHot); float4* shape = (float4*)(host + hdr.offShape);
+    float4* surf = (float4*)(host + hdr.offSurf); int* kind = (int*)(host + hdr.offKind);
+    for (uint32_t j = 0; j < count; j++) {
+        const VcrtSphere& s = spheres[order[j]];
+        shape[j] = make_float4(s.center[0], s.center[1], s.center[2], s.radius);
+        surf[j] = make_float4(s.colour[0], s.colour[1], s.colour[2], s.texture[1]);
+        kind[j] = (int)s.texture[0];   // switch(int(record.texture.x)), textures.glsl:66
+        if (j < scanCount) {
+            double cc = (double)s.center[0] * s.center[0] + (double)s.center[1] * s.center[1] + (double)s.center[2] * s.center[2];
+            double r2 = (double)s.radius * s.radius;
+            double inflated = (r2 + (double)kKappa * (cc + r2)) * (1.0 + 1.0 / 4194304.0);
+            float f = (float)inflated;
+            if ((double)f < inflated) f = nextafterf(f, INFINITY);
+            hot[j] = make_float4(s.center[0], s.center[1], s.center[2], f);
+        }
+    }
+    for (uint32_t j = scanCount; j < scanPad; j++) hot[j] = make_float4(0.f, 0.f, 0.f, -INFINITY);   // padding never passes
+    memcpy(host, &hdr, sizeof hdr);
+    delete[] order;
+
+    if (cudaComputeSceneBlob) { cudaFree(cudaComputeSceneBlob); cudaComputeSceneBlob = nullptr; }
+    cudaComputeSceneReady = false;
+    cudaError_t e = cudaMalloc(&cudaComputeSceneBlob, hdr.bytes);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(cudaComputeSceneBlob, host, hdr.bytes, cudaMemcpyHostToDevice, cudaComputeStream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(cudaComputeStream);
+    free(host);
+    if (e != cudaSuccess) return fail(VCRT_ERROR_CUDA, "scene upload: %s", cudaGetErrorString(e));
+    cudaComputeSceneHeader = hdr;
+    cudaComputeCamera = *camera;
+    cudaComputeSceneReady = true;
+    cudaComputeImageValid = false;
+    cudaComputeAccumulatedSamples = 0;
+    return VCRT_SUCCESS;
+}
+
+// shader.comp:18-39 in binary32, one rounding per operation (x86-64 host code has no FMA
+// contraction without -march flags; the build also passes -ffp-contract=off).
+static Frame makeFrame(const VcrtCamera& cam, uint32_t width, uint32_t height) {
+    struct H3 { float x, y, z; };
+    auto sub = [](H3 a, H3 b) { return H3{a.x - b.x, a.y - b.y, a.z - b.z}; };
+    auto lscale = [](float s, H3 a) { return H3{s * a.x, s * a.y, s * a.z}; };
+    auto divs = [](H3 a, float s) { return H3{a.x / s, a.y / s, a.z / s}; };
+    auto dot = [](H3 a, H3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; };
+    auto unit = [&](H3 a) { return divs(a, sqrtf(dot(a, a))); };
+    auto cross = [](H3 a, H3 b) { return H3{a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y}; };
+    auto add = [](H3 a, H3 b) { return H3{a.x + b.x, a.y + b.y, a.z + b.z}; };
+    H3 lookfrom{cam.lookfrom[0], cam.lookfrom[1], cam.lookfrom[2]}, lookat{cam.lookat[0], cam.lookat[1], cam.lookat[2]};
+    H3 vup{cam.vup[0], cam.vup[1], cam.vup[2]};
+    float focal_length = sqrtf(dot(sub(lookfrom, lookat), sub(lookfrom, lookat)));
+    float theta = cam.vfov * 0.017453292519943295f;
+    float h = tanf(theta / 2);
+    float viewport_height = 2 * h * focal_length;
+    float viewport_width = viewport_height * (float)(width / height);   // bug B1: integer division
+    H3 w = unit(sub(lookfrom, lookat));
+    H3 u = unit(cross(vup, w));
+    H3 v = cross(w, u);
+    H3 viewport_u = lscale(viewport_width, u);
+    H3 viewport_v = lscale(viewport_height, H3{-v.x, -v.y, -v.z});
+    H3 du = divs(viewport_u, (float)height);                            // bug B1: both deltas / HEIGHT
+    H3 dv = divs(viewport_v, (float)height);
+    H3 upper_left = sub(sub(sub(lookfrom, lscale(focal_length, w)), divs(viewport_u, 2.f)), divs(viewport_v, 2.f));
+    H3 p00 = add(upper_left, lscale(0.5f, add(du, dv)));
+    Frame f;
+    f.center = V3{lookfrom.x, lookfrom.y, lookfrom.z}; f.pixel00 = V3{p00.x, p00.y, p00.z};
+    f.du = V3{du.x, du.y, du.z}; f.dv = V3{dv.x, dv.y, dv.z};
+    return f;
+}
+
+// ------------------------------------------------------------------ small kernels
+// accumulated[p] = (keep ? accumulated[p] : 0) + plane[0][p] + plane[1][p] + ...   (fixed order)
+__global__ void combine_planes_kernel(float4* accumulated, const float4* planes, uint32_t pixels, uint32_t chunks, int keep) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pixels) return;
+    float4 a = keep ? accumulated[p] : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (uint32_t c = 0; c < chunks; c++) {
+        float4 s = planes[(size_t)c * pixels + p];
+        a.x = __fadd_rn(a.x, s.x); a.y = __fadd_rn(a.y, s.y); a.z = __fadd_rn(a.z, s.z);
+    }
+    accumulated[p] = a;
+}
+// shader.comp:56-57: color.rgb /= SAMPLES_PER_PIXEL; alpha stays 1 (shader.comp:44).
+__global__ void normalise_kernel(float4* image, const float4* sums, uint32_t pixels, float samples) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pixels) return;
+    float4 s = sums[p];
+    image[p] = make_float4(__fdiv_rn(s.x, samples), __fdiv_rn(s.y, samples), __fdiv_rn(s.z, samples), 1.0f);
+}
+// Fixed-point sums -> float sums (for cudaDownloadSums) and -> the normalised image.
+__global__ void fixed_to_float_kernel(float4* sums, const long long* fixedSums, uint32_t pixels) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pixels) return;
+    const long long* f = fixedSums + 4 * (size_t)p;
+    const double s = 1.0 / 4294967296.0;
+    sums[p] = make_float4((float)((double)f[0] * s), (float)((double)f[1] * s), (float)((double)f[2] * s), 0.f);
+}
+__global__ void normalise_fixed_kernel(float4* image, const long long* fixedSums, uint32_t pixels, double samples) {
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pixels) return;
+    const long long* f = fixedSums + 4 * (size_t)p;
+    const double s = 1.0 / (4294967296.0 * samples);
+    image[p] = make_float4((float)((double)f[0] * s), (float)((double)f[1] * s), (float)((double)f[2] * s), 1.0f);
+}
+// FFMA-only kernel: the measured FP32 roofline denominator.
+__global__ void fp32_peak_kernel(float* out, int iters, float a, float b, long long* cycles) {
+    float x[8];
+#pragma unroll
+    for (int c = 0; c < 8; c++) x[c] = threadIdx.x * 1e-3f + c;
+    long long t0 = clock64();
+#pragma unroll 1
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+#pragma unroll
+            for (int c = 0; c < 8; c++) x[c] = fmaf(x[c], a, b);
+    }
+    long long t1 = clock64();
+    float s = 0;
+#pragma unroll
+    for (int c = 0; c < 8; c++) s += x[c];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+    if (threadIdx.x == 0 && blockIdx.x == 0) *cycles = t1 - t0;
+}
+
+extern "C" int cudaMeasureFp32Peak(OUT double* tflops, OUT double* smClockMHz) {
+    int rc = ensureDevice();
+    if (rc) return rc;
+    const int threads = 512, blocks = cudaComputeSmCount * 4, iters = 8192;
+    float* out = nullptr; long long* cycles = nullptr;
+    CUDA_TRY(cudaMalloc(&out, sizeof(float) * threads * blocks));
+    CUDA_TRY(cudaMalloc(&cycles, sizeof(long long)));
+    float best = 1e30f;
+    for (int rep = 0; rep < 6; rep++) {
+        CUDA_TRY(cudaEventRecord(cudaComputeEvents[2], cudaComputeStream));
+        fp32_peak_kernel<<<blocks, threads, 0, cudaComputeStream>>>(out, iters, 1.0001f, 1e-4f, cycles);
+        CUDA_TRY(cudaEventRecord(cudaComputeEvents[3], cudaComputeStream));
+        CUDA_TRY(cudaEventSynchronize(cudaComputeEvents[3]));
+        float ms = 0; CUDA_TRY(cudaEventElapsedTime(&ms, cudaComputeEvents[2], cudaComputeEvents[3]));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    long long hostCycles = 0;
+    CUDA_TRY(cudaMemcpy(&hostCycles, cycles, sizeof hostCycles, cudaMemcpyDeviceToHost));
+    cudaFree(out); cudaFree(cycles);
+    double flop = (double)threads * blocks * iters * 64.0 * 2.0;
+    if (tflops) *tflops = flop / (best * 1e-3) * 1e-12;
+    // one block's loop = 4 resident blocks/SM x 16 warps sharing 4 schedulers: cycles are wall cycles of that SM
+    if (smClockMHz) *smClockMHz = (double)hostCycles / (best * 1e-3) * 1e-6;
+    return VCRT_SUCCESS;
+}
+
+// ------------------------------------------------------------------ buffers
+static int ensureImageBuffers(uint32_t width, uint32_t height, uint32_t chunks) {
+    const size_t pixels = (size_t)width * height;
+    if (width != cudaComputeImageWidth || height != cudaComputeImageHeight) {
+        if (cudaComputeAccumulated) cudaFree(cudaComputeAccumulated);
+        if (cudaComputeReduced) cudaFree(cudaComputeReduced);
+        if (cudaComputeResultImage) cudaFree(cudaComputeResultImage);
+        if (cudaComputeFixedSums) cudaFree(cudaComputeFixedSums);
+        if (cudaComputeFixedReduced) cudaFree(cudaComputeFixedReduced);
+        cudaComputeFixedSums = cudaComputeFixedReduced = nullptr;
+        cudaComputeAccumulated = cudaComputeReduced = cudaComputeResultImage = nullptr;
+        cudaComputeImageWidth = cudaComputeImageHeight = 0;
+        cudaComputeImageValid = false; cudaComputeAccumulatedSamples = 0;
+        CUDA_TRY(cudaMalloc(&cudaComputeAccumulated, pixels * sizeof(float4)));
+        CUDA_TRY(cudaMalloc(&cudaComputeReduced, pixels * sizeof(float4)));
+        CUDA_TRY(cudaMalloc(&cudaComputeResultImage, pixels * sizeof(float4)));
+        CUDA_TRY(cudaMalloc(&cudaComputeFixedSums, pixels * 4 * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&cudaComputeFixedReduced, pixels * 4 * sizeof(long long)));
+        cudaComputeImageWidth = width; cudaComputeImageHeight = height;
+    }
+    const size_t need = pixels * sizeof(float4) * chunks;
+    if (need > cudaComputeSumPlanesBytes) {
+        if (cudaComputeSumPlanes) cudaFree(cudaComputeSumPlanes);
+        cudaComputeSumPlanes = nullptr; cudaComputeSumPlanesBytes = 0;
+        CUDA_TRY(cudaMalloc(&cudaComputeSumPlanes, need));
+        cudaComputeSumPlanesBytes = need;
+    }
+    return VCRT_SUCCESS;
+}
+
+// ------------------------------------------------------------------ NCCL (loaded lazily; single-GPU use never touches it)
+#include <nccl.h>
+static void* ncclLibrary = nullptr;
+static ncclComm_t cudaComputeComm = nullptr;
+static int cudaComputeRank = 0, cudaComputeWorldSize = 1;
+static ncclResult_t (*pNcclGetUniqueId)(ncclUniqueId*) = nullptr;
+static ncclResult_t (*pNcclCommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+static ncclResult_t (*pNcclCommDestroy)(ncclComm_t) = nullptr;
+static ncclResult_t (*pNcclReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+static ncclResult_t (*pNcclAllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+static const char* (*pNcclGetErrorString)(ncclResult_t) = nullptr;
+static float* cudaComputeCommScratch = nullptr;
+
+static int ensureNccl(void) {
+    if (ncclLibrary) return VCRT_SUCCESS;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (int i = 0; i < 2 && !ncclLibrary; i++) ncclLibrary = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
+    if (!ncclLibrary) return fail(VCRT_ERROR_NCCL, "cannot load libnccl: %s", dlerror());
+#define NCCL_SYM(ptr, name) *(void**)(&ptr) = dlsym(ncclLibrary, name); if (!ptr) return fail(VCRT_ERROR_NCCL, "libnccl lacks %s", name)
+    NCCL_SYM(pNcclGetUniqueId, "ncclGetUniqueId"); NCCL_SYM(pNcclCommInitRank, "ncclCommInitRank");
+    NCCL_SYM(pNcclCommDestroy, "ncclCommDestroy"); NCCL_SYM(pNcclReduce, "ncclReduce");
+    NCCL_SYM(pNcclAllReduce, "ncclAllReduce"); NCCL_SYM(pNcclGetErrorString, "ncclGetErrorString");
+#undef NCCL_SYM
+    return VCRT_SUCCESS;
+}
+#define NCCL_TRY(expr) do { ncclResult_t ncclTryResult = (expr); if (ncclTryResult != ncclSuccess) return fail(VCRT_ERROR_NCCL, #expr ": %s", pNcclGetErrorString(ncclTryResult)); } while (0)
+
+extern "C" int cudaCommGetUniqueId(OUT void* id128) {
+    if (!id128) return fail(VCRT_ERROR_INVALID_ARGUMENT, "null id%s", "");
+    int rc = ensureNccl(); if (rc) return rc;
+    ncclUniqueId id; NCCL_TRY(pNcclGetUniqueId(&id));
+    memcpy(id128, &id, sizeof id);   // NCCL_UNIQUE_ID_BYTES == 128
+    return VCRT_SUCCESS;
+}
+extern "C" int cudaCommInitRank(IN const void* id128, IN int rank, IN int worldSize) {
+    if (!id128 || worldSize < 1 || rank < 0 || rank >= worldSize) return fail(VCRT_ERROR_INVALID_ARGUMENT, "bad communicator arguments%s", "");
+    int rc = ensureDevice(); if (rc) return rc;
+    rc = ensureNccl(); if (rc) return rc;
+    if (cudaComputeComm) { pNcclCommDestroy(cudaComputeComm); cudaComputeComm = nullptr; }
+    ncclUniqueId id; memcpy(&id, id128, sizeof id);
+    NCCL_TRY(pNcclCommInitRank(&cudaComputeComm, worldSize, id, rank));
+    cudaComputeRank = rank; cudaComputeWorldSize = worldSize;
+    if (!cudaComputeCommScratch) CUDA_TRY(cudaMalloc(&cudaComputeCommScratch, 64));
+    return VCRT_SUCCESS;
+}
+extern "C" int cudaCommDestroy(void) {
+    if (cudaComputeComm && pNcclCommDestroy) pNcclCommDestroy(cudaComputeComm);
+    cudaComputeComm = nullptr; cudaComputeRank = 0; cudaComputeWorldSize = 1;
+    return VCRT_SUCCESS;
+}
+extern "C" int cudaCommMaxFloat(IN float value, OUT float* maxValue) {
+    if (!maxValue) return fail(VCRT_ERROR_INVALID_ARGUMENT, "null output%s", "");
+    if (!cudaComputeComm) { *maxValue = value; return VCRT_SUCCESS; }
+    CUDA_TRY(cudaMemcpyAsync(cudaComputeCommScratch, &value, sizeof value, cudaMemcpyHostToDevice, cudaComputeStream));
+    NCCL_TRY(pNcclAllReduce(cudaComputeCommScratch, cudaComputeCommScratch, 1, ncclFloat, ncclMax, cudaComputeComm, cudaComputeStream));
+    CUDA_TRY(cudaMemcpyAsync(maxValue, cudaComputeCommScratch, sizeof value, cudaMemcpyDeviceToHost, cudaComputeStream));
+    CUDA_TRY(cudaStreamSynchronize(cudaComputeStream));
+    return VCRT_SUCCESS;
+}
+extern "C" int cudaCommBarrier(void) { float v = 0.f, m; return cudaCommMaxFloat(v, &m); }
+
+// ------------------------------------------------------------------ render dispatch
+template <int THREADS, int PAIRS, int CAP, bool FIXED>
+static int launchScan(const RenderArgs& args, uint32_t* launches) {
+    using Cfg = ScanConfig<THREADS, PAIRS, CAP>;
+    const size_t smem = Cfg::smem_bytes(cudaComputeSceneHeader.bytes);
+    auto kernel = render_scan_kernel<THREADS, PAIRS, CAP, FIXED>;
+    CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned int grid = (unsigned int)cudaComputeSmCount;   // persistent: one CTA per SM
+    const unsigned int firstDynamicItem = grid * Cfg::R * THREADS;
+    CUDA_TRY(cudaMemcpyAsync(cudaComputeWorkCounter, &firstDynamicItem, sizeof firstDynamicItem, cudaMemcpyHostToDevice, cudaComputeStream));
+    kernel<<<grid, THREADS, smem, cudaComputeStream>>>(cudaComputeSceneBlob, args);
+    CUDA_TRY(cudaGetLastError());
+    *launches += 1;
+    return VCRT_SUCCESS;
+}
+
+static const size_t kSmemBudget = 227 * 1024;
+static bool scanFits(int threads, int pairs, int cap) {
+    size_t state = (size_t)SF_COUNT * 2 * pairs * threads * 4, lists = (size_t)(cap + 2) * 2 * pairs * threads * 2;
+    return 16 + (size_t)cudaComputeSceneHeader.bytes + state + lists <= kSmemBudget && cudaComputeSceneHeader.scanPad < 65536u;
+}
+
+extern "C" int cudaRender(IN const VcrtRenderParams* p) {
+    if (!p) return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRender: null params%s", "");
+    if (!p->width || !p->height || !p->samplesPerPixel || p->width > 65535u || p->height > 65535u || p->samplesPerPixel >= (1u << 24))
+        return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRender: width/height must be 1..65535 and samplesPerPixel 1..2^24-1%s", "");
+    int rc = ensureDevice(); if (rc) return rc;
+    if (!cudaComputeSceneReady) return fail(VCRT_ERROR_NOT_READY, "cudaRender before cudaUploadScene%s", "");
+
+    uint32_t traversal = p->traversal;
+    if (traversal == VCRT_TRAVERSAL_AUTO) traversal = scanFits(256, 2, 12) ? VCRT_TRAVERSAL_BRUTE : VCRT_TRAVERSAL_SIMPLE;
+    if (traversal == VCRT_TRAVERSAL_LBVH) return fail(VCRT_ERROR_UNSUPPORTED, "LBVH traversal is not built yet%s", "");
+    if (traversal == VCRT_TRAVERSAL_BRUTE && !scanFits(256, 2, 12))
+        return fail(VCRT_ERROR_UNSUPPORTED, "scene does not fit shared memory for VCRT_TRAVERSAL_BRUTE%s", "");
+    if (traversal > VCRT_TRAVERSAL_SIMPLE) return fail(VCRT_ERROR_INVALID_ARGUMENT, "unknown traversal%s", "");
+
+    const bool wide = scanFits(512, 2, 12);
+    const uint32_t pixels = p->width * p->height;
+    // Accumulation mode.  sampleChunks == 0 (default, brute force only): 32.32 fixed-point sums, every sample added
+    // with an integer RED, work items of a few samples each -> good load balance and bits that do not depend on the
+    // schedule or the GPU count.  sampleChunks >= 1: float sums in strict sample order per chunk (1 = the oracle's order).
+    uint32_t chunks = 1;
+    bool fixedMode = false;
+    if (traversal == VCRT_TRAVERSAL_BRUTE) {
+        chunks = p->sampleChunks;
+        fixedMode = chunks == 0;
+        if (chunks > p->samplesPerPixel) chunks = p->samplesPerPixel;
+        if (chunks < 1u) chunks = 1u;
+    }
+    const uint32_t samplesPerItem = p->reserved[0] ? p->reserved[0] : 1u;   // measured: 1 is fastest (keeps the lanes of a warp on neighbouring pixels)
+    rc = ensureImageBuffers(p->width, p->height, chunks); if (rc) return rc;
+    const bool keep = (p->flags & VCRT_FLAG_ACCUMULATE) && cudaComputeAccumulatedSamples > 0;
+    if (keep && fixedMode != cudaComputeAccumulatedIsFixed)
+        return fail(VCRT_ERROR_UNSUPPORTED, "VCRT_FLAG_ACCUMULATE across different accumulation modes%s", "");
+
+    RenderArgs args; memset(&args, 0, sizeof args);
+    args.frame = makeFrame(cudaComputeCamera, p->width, p->height);
+    args.width = p->width; args.height = p->height; args.spp = p->samplesPerPixel; args.sampleOffset = p->sampleOffset;
+    args.maxDepth = p->maxDepth; args.seedLo = (uint32_t)p->seed; args.seedHi = (uint32_t)(p->seed >> 32);
+    args.chunks = chunks; args.flags = p->flags; args.sums = cudaComputeSumPlanes;
+    args.fixedSums = cudaComputeFixedSums; args.samplesPerItem = samplesPerItem;
+    args.counters = cudaComputeCounters; args.workCounter = cudaComputeWorkCounter;
+
+    uint32_t launches = 0;
+    CUDA_TRY(cudaEventRecord(cudaComputeEvents[0], cudaComputeStream));
+    CUDA_TRY(cudaMemsetAsync(cudaComputeCounters, 0, sizeof(unsigned long long) * CTR_COUNT, cudaComputeStream));
+    CUDA_TRY(cudaEventRecord(cudaComputeEvents[1], cudaComputeStream));
+    if (fixedMode && !keep) CUDA_TRY(cudaMemsetAsync(cudaComputeFixedSums, 0, (size_t)pixels * 4 * sizeof(long long), cudaComputeStream));
+    if (p->maxDepth == 0) {   // no pass of functions.glsl:73 runs: every sample is black (bug B7)
+        CUDA_TRY(cudaMemsetAsync(cudaComputeSumPlanes, 0, (size_t)pixels * sizeof(float4) * chunks, cudaComputeStream));
+    } else if (traversal == VCRT_TRAVERSAL_SIMPLE) {
+        DeviceScene scene; memset(&scene, 0, sizeof scene);
+        scene.shape = (const float4*)(cudaComputeSceneBlob + cudaComputeSceneHeader.offShape);
+        scene.surf = (const float4*)(cudaComputeSceneBlob + cudaComputeSceneHeader.offSurf);
+        scene.kind = (const int*)(cudaComputeSceneBlob + cudaComputeSceneHeader.offKind);
+        scene.count = (int)cudaComputeSceneHeader.count;
+        dim3 grid((p->width + 15) / 16, (p->height + 7) / 8);
+        render_simple_kernel<<<grid, 128, 0, cudaComputeStream>>>(scene, args);
+        CUDA_TRY(cudaGetLastError());
+        launches++;
+    } else {
+        if (fixedMode) rc = wide ? launchScan<512, 2, 12, true>(args, &launches) : launchScan<256, 2, 12, true>(args, &launches);
+        else rc = wide ? launchScan<512, 2, 12, false>(args, &launches) : launchScan<256, 2, 12, false>(args, &launches);
+        if (rc) return rc;
+    }
+    CUDA_TRY(cudaEventRecord(cudaComputeEvents[2], cudaComputeStream));
+
+    const unsigned int pixelBlocks = (pixels + 255) / 256;
+    if (fixedMode && p->maxDepth != 0) fixed_to_float_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeAccumulated, cudaComputeFixedSums, pixels);
+    else combine_planes_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeAccumulated, cudaComputeSumPlanes, pixels, chunks, keep ? 1 : 0);
+    launches++;
+    const bool fixedSums = fixedMode && p->maxDepth != 0;
+    cudaComputeAccumulatedSamples = (keep ? cudaComputeAccumulatedSamples : 0) + p->samplesPerPixel;
+    cudaComputeAccumulatedIsFixed = fixedMode;
+
+    const float4* finalSums = cudaComputeAccumulated;
+    const long long* finalFixed = cudaComputeFixedSums;
+    uint64_t totalSamples = cudaComputeAccumulatedSamples;
+    bool haveImage = true;
+    if (cudaComputeComm && cudaComputeWorldSize > 1 && !(p->flags & VCRT_FLAG_NO_REDUCE)) {
+        // The one exchange of the path: sum the per-GPU accumulation buffers over NVLink.
+        const void* src = fixedSums ? (const void*)cudaComputeFixedSums : (const void*)cudaComputeAccumulated;
+        void* dst = fixedSums ? (void*)cudaComputeFixedReduced : (void*)cudaComputeReduced;
+        const ncclDataType_t type = fixedSums ? ncclInt64 : ncclFloat;
+        const size_t elements = (size_t)pixels * 4;
+        if (p->flags & VCRT_FLAG_ALL_REDUCE) NCCL_TRY(pNcclAllReduce(src, dst, elements, type, ncclSum, cudaComputeComm, cudaComputeStream));
+        else NCCL_TRY(pNcclReduce(src, dst, elements, type, ncclSum, 0, cudaComputeComm, cudaComputeStream));
+        finalSums = cudaComputeReduced; finalFixed = cudaComputeFixedReduced;
+        totalSamples *= (uint64_t)cudaComputeWorldSize;   // equal shards unless the caller says otherwise
+        haveImage = (p->flags & VCRT_FLAG_ALL_REDUCE) || cudaComputeRank == 0;
+    }
+    if (p->totalSamples) totalSamples = p->totalSamples;
+    if (haveImage) {
+        if (fixedSums) normalise_fixed_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeResultImage, finalFixed, pixels, (double)totalSamples);
+        else normalise_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeResultImage, finalSums, pixels, (float)totalSamples);
+        launches++;
+    }
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaEventRecord(cudaComputeEvents[3], cudaComputeStream));
+    CUDA_TRY(cudaStreamSynchronize(cudaComputeStream));   // the frame is complete when we return (platform/Linux.cpp:365)
+    cudaComputeImageValid = haveImage;
+
+    unsigned long long ctr[CTR_COUNT];
+    CUDA_TRY(cudaMemcpy(ctr, cudaComputeCounters, sizeof ctr, cudaMemcpyDeviceToHost));
+    VcrtRenderStats& st = cudaComputeLastStats; memset(&st, 0, sizeof st);
+    st.samples = (uint64_t)pixels * p->samplesPerPixel;
+    st.rays = ctr[CTR_RAYS]; st.depthExhausted = ctr[CTR_EXHAUSTED]; st.badMaterial = ctr[CTR_BAD_MATERIAL];
+    st.candidates = ctr[CTR_CANDIDATES]; st.listOverflows = ctr[CTR_OVERFLOWS];
+    st.sphereTests = st.rays * cudaComputeSceneHeader.count; st.nodeVisits = ctr[CTR_NODES];
+    for (int i = 0; i < 4; i++) st.hitsByMaterial[i] = ctr[CTR_HITS0 + i];
+    for (int i = 0; i < 8; i++) st.pathLength[i] = ctr[CTR_PATH0 + i];
+    CUDA_TRY(cudaEventElapsedTime(&st.renderKernelMs, cudaComputeEvents[1], cudaComputeEvents[2]));
+    CUDA_TRY(cudaEventElapsedTime(&st.totalMs, cudaComputeEvents[0], cudaComputeEvents[3]));
+    st.kernelLaunches = launches; st.traversalUsed = traversal; st.sampleChunksUsed = chunks;
+    if (st.badMaterial) return fail(VCRT_ERROR_SCENE, "scene has texture ids outside 1..3 (hits on them were absorbed)%s", "");
+    return VCRT_SUCCESS;
+}
+
+extern "C" int cudaGetRenderStats(OUT VcrtRenderStats* stats) {
+    if (!stats) return fail(VCRT_ERROR_INVALID_ARGUMENT, "null stats%s", "");
+    *stats = cudaComputeLastStats;
+    return VCRT_SUCCESS;
+}
+
+static int downloadBuffer(const float4* src, bool valid, float* rgba, size_t bytes) {
+    if (!rgba) return fail(VCRT_ERROR_INVALID_ARGUMENT, "null destination%s", "");
+    if (!valid || !src) return fail(VCRT_ERROR_NOT_READY, "no rendered image on this device%s", "");
+    const size_t need = (size_t)cudaComputeImageWidth * cudaComputeImageHeight * sizeof(float4);
+    if (bytes < need) return fail(VCRT_ERROR_INVALID_ARGUMENT, "destination smaller than width*height*16 bytes%s", "");
+    CUDA_TRY(cudaMemcpyAsync(rgba, src, need, cudaMemcpyDeviceToHost, cudaComputeStream));
+    CUDA_TRY(cudaStreamSynchronize(cudaComputeStream));
+    return VCRT_SUCCESS;
+}
+extern "C" int cudaDownloadImage(OUT float* rgba, IN size_t bytes) { return downloadBuffer(cudaComputeResultImage, cudaComputeImageValid, rgba, bytes); }
+extern "C" int cudaDownloadSums(OUT float* rgba, IN size_t bytes) { return downloadBuffer(cudaComputeAccumulated, cudaComputeAccumulatedSamples > 0, rgba, bytes); }
+
+extern "C" int cudaGetDeviceImage(OUT void** devicePointer, OUT size_t* bytes) {
+    if (!devicePointer || !bytes) return fail(VCRT_ERROR_INVALID_ARGUMENT, "null output%s", "");
+    if (!cudaComputeImageValid) return fail(VCRT_ERROR_NOT_READY, "no rendered image on this device%s", "");
+    *devicePointer = cudaComputeResultImage; *bytes = (size_t)cudaComputeImageWidth * cudaComputeImageHeight * sizeof(float4);
+    return VCRT_SUCCESS;
+}
+extern "C" int cudaGetDeviceSums(OUT void** devicePointer, OUT size_t* bytes) {
+    if (!devicePointer || !bytes) return fail(VCRT_ERROR_INVALID_ARGUMENT, "null output%s", "");
+    if (!cudaComputeAccumulated || !cudaComputeAccumulatedSamples) return fail(VCRT_ERROR_NOT_READY, "nothing rendered yet%s", "");
+    *devicePointer = cudaComputeAccumulated; *bytes = (size_t)cudaComputeImageWidth * cudaComputeImageHeight * sizeof(float4);
+    return VCRT_SUCCESS;
+}
+
+// Tolerates never-created state, like EndRenderingOperation's null checks (Renderer.cpp:716-773).
+extern "C" int cudaDestroyRenderer(void) {
+    cudaCommDestroy();
+    if (cudaComputeDeviceReady) {
+        cudaSetDevice(cudaComputeDevice);
+        if (cudaComputeStream) cudaStreamSynchronize(cudaComputeStream);
+        void* buffers[] = {cudaComputeSceneBlob, cudaComputeSumPlanes, cudaComputeAccumulated, cudaComputeReduced, cudaComputeFixedSums, cudaComputeFixedReduced,
+                           cudaComputeResultImage, cudaComputeCounters, cudaComputeWorkCounter, cudaComputeCommScratch};
+        for (void* b : buffers) if (b) cudaFree(b);
+        for (int i = 0; i < 4; i++) if (cudaComputeEvents[i]) cudaEventDestroy(cudaComputeEvents[i]);
+        if (cudaComputeStream) cudaStreamDestroy(cudaComputeStream);
+    }
+    cudaComputeSceneBlob = nullptr; cudaComputeSumPlanes = nullptr; cudaComputeSumPlanesBytes = 0;
+    cudaComputeAccumulated = cudaComputeReduced = cudaComputeResultImage = nullptr;
+    cudaComputeFixedSums = cudaComputeFixedReduced = nullptr;
+    cudaComputeCounters = nullptr; cudaComputeWorkCounter = nullptr; cudaComputeCommScratch = nullptr;
+    cudaComputeStream = nullptr; for (int i = 0; i < 4; i++) cudaComputeEvents[i] = nullptr;
+    cudaComputeImageWidth = cudaComputeImageHeight = 0; cudaComputeAccumulatedSamples = 0;
+    cudaComputeImageValid = false; cudaComputeSceneReady = false; cudaComputeDeviceReady = false;
+    return VCRT_SUCCESS;
+}

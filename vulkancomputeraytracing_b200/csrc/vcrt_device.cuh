@@ -1,0 +1,114 @@
+/* @file vcrt_device.cuh
+
+    Device-side vocabulary of the path tracer: IEEE binary32 helpers that never contract,
+    Philox4x32-10, the scene / frame / work descriptors, the exact ray-sphere test and the
+    three material scatter routines.
+    SPDX-License-Identifier: WTFPL
+
+    Arithmetic policy.  Everything that decides WHAT a path does (roots, hit points, normals,
+    scatter directions, attenuation) is written with the *_rn intrinsics below, one rounding per
+    operation in the order of the reference's GLSL statements, so nvcc can neither fuse nor
+    reorder it.  Only the conservative candidate filter of the brute-force scan
+    (vcrt_scan.cuh) uses fused packed FMAs, and it can only ever ADD spheres to the set that
+    is then tested exactly.
+*/
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define VCRT_DEV __device__ __forceinline__
+
+namespace vcrt {
+
+// ------------------------------------------------------------------ exact binary32
+VCRT_DEV float fadd(float a, float b) { return __fadd_rn(a, b); }
+VCRT_DEV float fsub(float a, float b) { return __fsub_rn(a, b); }
+VCRT_DEV float fmul(float a, float b) { return __fmul_rn(a, b); }
+// IEEE division and square root expand to ~15 instructions plus a slow-path call each; the path
+// shader uses ~50 of them once per ray, so they are real functions (one copy in the instruction
+// cache) rather than inlined at every site.
+__device__ __noinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __noinline__ float fsqrt(float a) { return __fsqrt_rn(a); }
+
+struct V3 { float x, y, z; };
+VCRT_DEV V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+VCRT_DEV V3 vadd(V3 a, V3 b) { return v3(fadd(a.x, b.x), fadd(a.y, b.y), fadd(a.z, b.z)); }
+VCRT_DEV V3 vsub(V3 a, V3 b) { return v3(fsub(a.x, b.x), fsub(a.y, b.y), fsub(a.z, b.z)); }
+VCRT_DEV V3 vmul(V3 a, V3 b) { return v3(fmul(a.x, b.x), fmul(a.y, b.y), fmul(a.z, b.z)); }
+VCRT_DEV V3 vscale(V3 a, float s) { return v3(fmul(a.x, s), fmul(a.y, s), fmul(a.z, s)); }
+VCRT_DEV V3 vdiv(V3 a, float s) { return v3(fdiv(a.x, s), fdiv(a.y, s), fdiv(a.z, s)); }
+VCRT_DEV V3 vneg(V3 a) { return v3(-a.x, -a.y, -a.z); }
+// GLSL dot(): (x*x' + y*y') + z*z'
+VCRT_DEV float vdot(V3 a, V3 b) { return fadd(fadd(fmul(a.x, b.x), fmul(a.y, b.y)), fmul(a.z, b.z)); }
+// GLSL normalize(): v / length(v)
+VCRT_DEV V3 vunit(V3 a) { return vdiv(a, fsqrt(vdot(a, a))); }
+// GLSL reflect(): I - 2*dot(N,I)*N
+VCRT_DEV V3 vreflect(V3 i, V3 n) { return vsub(i, vscale(n, fmul(2.0f, vdot(n, i)))); }
+
+// ------------------------------------------------------------------ Philox4x32-10
+// Counter-based generator (Salmon et al., SC'11).  counter = (pixel index, global sample
+// index, draw block, 0), key = the 64-bit seed.  Draw block 0 = the two pixel-jitter draws of
+// shader.comp:48; block k >= 1 = the draws of the k-th scatter event (functions.glsl:42-44,
+// textures.glsl:51).  The oracle's PHILOX mode uses the identical layout.
+VCRT_DEV void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+    for (int round = 0; round < 10; round++) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+VCRT_DEV float u01(uint32_t bits) { return fmul((float)(bits >> 8), 5.9604644775390625e-08f); }  // [0,1), 24 bits
+
+// ------------------------------------------------------------------ descriptors
+// Scene as a structure of arrays (one float4 per sphere per array), built by cudaUploadScene
+// from the VcrtSphere AoS:
+//   hot[i]   = (cx, cy, cz, r^2 inflated by the filter margin)   <- the only array the scan streams
+//   shape[i] = (cx, cy, cz, r)                                  <- exact test + normal
+//   surf[i]  = (colour r, g, b, texture.y)                      <- attenuation + parameter
+//   kind[i]  = int(texture.x)                                   <- material id
+struct DeviceScene {
+    const float4* hot;
+    const float4* shape;
+    const float4* surf;
+    const int* kind;
+    const int* always;   // indices of "huge" spheres kept out of the filter scan (tested exactly for every ray)
+    int count;           // all spheres
+    int scanCount;       // spheres in hot[] order that the filter scans (= count - alwaysCount), padded entries never pass
+    int alwaysCount;
+    const int* scanIndex;  // scanIndex[j] = original sphere index of hot[j]
+};
+
+// Camera frame of shader.comp:18-39, computed once on the host in the same binary32 order.
+struct Frame { V3 center, pixel00, du, dv; };
+
+struct RenderArgs {
+    Frame frame;
+    uint32_t width, height;
+    uint32_t spp;           // samples per pixel rendered by this launch
+    uint32_t sampleOffset;  // global index of the first of them
+    uint32_t maxDepth;
+    uint32_t seedLo, seedHi;
+    uint32_t chunks;        // a pixel's spp split into this many work items (partial-sum planes)
+    uint32_t flags;
+    float4* sums;           // float modes: [chunks][height*width] (x,y,z = sums, w unused)
+    long long* fixedSums;   // fixed-point mode: [height*width][4] signed 32.32 sums (r, g, b, unused)
+    uint32_t samplesPerItem;  // fixed-point mode: samples per work item
+    unsigned long long* counters;  // see Counter enum
+    unsigned int* workCounter;     // dynamic item dispenser
+};
+
+enum Counter { CTR_RAYS = 0, CTR_EXHAUSTED, CTR_BAD_MATERIAL, CTR_CANDIDATES, CTR_OVERFLOWS, CTR_TESTS, CTR_NODES,
+               CTR_HITS0, CTR_HITS1, CTR_HITS2, CTR_HITS3, CTR_PATH0, CTR_COUNT = CTR_PATH0 + 8 };
+
+struct Ray { V3 o, d; };
+struct HitRec { float t; int index; };  // nearest accepted root and its sphere (index < 0: none)
+
+constexpr float kTMin = 0.001f;   // functions.glsl:75
+constexpr float kTMax = 1e5f;     // globals.glsl:26 `infinity`
+constexpr float kFixedOne = 4294967296.0f;   // 2^32: radiance sums are exact integers in units of 2^-32
+
+}  // namespace vcrt

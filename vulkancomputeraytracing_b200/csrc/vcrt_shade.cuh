@@ -1,0 +1,117 @@
+/* @file vcrt_shade.cuh
+
+    Exact ray-sphere test, primary-ray generation, the three materials and the sky:
+    the parts of the path that are evaluated once per ray (not once per ray per sphere).
+    SPDX-License-Identifier: WTFPL
+*/
+#pragma once
+#include "vcrt_device.cuh"
+
+namespace vcrt {
+
+// functions.glsl:14-33 for one sphere, `a` = dot(d,d) hoisted by the caller (same value every
+// time the reference recomputes it).  Updates rec when this sphere gives a nearer accepted root.
+VCRT_DEV void hit_exact(float4 shape, int index, const Ray& r, float a, HitRec& rec) {
+    V3 oc = vsub(r.o, v3(shape.x, shape.y, shape.z));
+    float half_b = vdot(oc, r.d);
+    float c = fsub(vdot(oc, oc), fmul(shape.w, shape.w));
+    float disc = fsub(fmul(half_b, half_b), fmul(a, c));
+    if (disc < 0) return;
+    float sqrtd = fsqrt(disc);
+    float root = fdiv(fsub(-half_b, sqrtd), a);
+    if (root <= kTMin || rec.t <= root) {
+        root = fdiv(fadd(-half_b, sqrtd), a);
+        if (root <= kTMin || rec.t <= root) return;
+    }
+    rec.t = root;
+    rec.index = index;
+}
+
+// shader.comp:42-52: the camera ray of pixel (px,py), sample jitter (ju,jv) in [0,1).
+VCRT_DEV Ray primary_ray(const Frame& f, uint32_t px, uint32_t py, float ju, float jv) {
+    V3 pixel_center = vadd(vadd(f.pixel00, vscale(f.du, (float)px)), vscale(f.dv, (float)py));
+    V3 random_square = vadd(vscale(f.du, fadd(-0.5f, ju)), vscale(f.dv, fadd(-0.5f, jv)));
+    V3 pixel_sample = vadd(pixel_center, random_square);
+    Ray r; r.o = f.center; r.d = vsub(pixel_sample, f.center);  // never normalised (bug B3)
+    return r;
+}
+
+// functions.glsl:85-89: sky colour seen along d.  mix(vec3(1), vec3(.5,.7,1), a)
+VCRT_DEV V3 sky(V3 d) {
+    V3 unit_direction = vunit(d);
+    float a = fmul(0.5f, fadd(unit_direction.y, 1.0f));
+    float ia = fsub(1.0f, a);
+    return v3(fadd(fmul(1.f, ia), fmul(.5f, a)), fadd(fmul(1.f, ia), fmul(.7f, a)), fadd(fmul(1.f, ia), fmul(1.f, a)));
+}
+
+// functions.glsl:42-44 with the three hash draws replaced by Philox draws (bug B4 kept:
+// a unit vector in the positive octant).
+VCRT_DEV V3 random_in_unit_sphere(const float u[4]) { return vunit(v3(u[0], u[1], u[2])); }
+
+// functions.glsl:46-56
+VCRT_DEV bool modified_refract(V3 v, V3 n, float ni_over_nt, V3& refracted) {
+    float dt = vdot(v, n);
+    float disc = fsub(1.f, fmul(fmul(ni_over_nt, ni_over_nt), fsub(1.f, fmul(dt, dt))));
+    if (disc > 0.f) {
+        V3 lhs = vscale(vsub(v, vscale(n, dt)), ni_over_nt);
+        refracted = vsub(lhs, vscale(n, fsqrt(disc)));
+        return true;
+    }
+    return false;
+}
+
+// functions.glsl:58-62.  pow(x, 5.) as four multiplies: same sign and NaN behaviour as C powf
+// for the negative bases the unnormalised cosine produces (bug B6 -> "refract").
+VCRT_DEV float schlick(float cosine, float ior) {
+    float r0 = fdiv(fsub(1.f, ior), fadd(1.f, ior));
+    r0 = fmul(r0, r0);
+    float x = fsub(1.f, cosine);
+    float x2 = fmul(x, x);
+    float x5 = fmul(fmul(x2, x2), x);
+    return fadd(r0, fmul(fsub(1.f, r0), x5));
+}
+
+// textures.glsl:19-71.  Scatters `ray` at a hit on sphere `index` at parameter t; multiplies
+// `colour` (the path throughput) by the attenuation.  Returns false for a texture id outside
+// 1..3 (reference: silent no-op that re-hits until the depth runs out; here: absorbed + counted).
+VCRT_DEV bool scatter(const float4 shape, const float4 surf, int kind, float t, Ray& ray, V3& colour, const float u[4]) {
+    V3 point = vadd(vscale(ray.d, t), ray.o);                                   // functions.glsl:35
+    V3 normal = vdiv(vsub(point, v3(shape.x, shape.y, shape.z)), shape.w);      // functions.glsl:36, outward
+    V3 albedo = v3(surf.x, surf.y, surf.z);
+    float param = surf.w;
+    if (kind == 1) {  // lambertian, textures.glsl:19-25 (bug B4b: extra * texture.y)
+        V3 direction = vadd(normal, random_in_unit_sphere(u));
+        colour = vscale(vmul(colour, albedo), param);
+        ray.o = point; ray.d = direction;
+        return true;
+    }
+    if (kind == 2) {  // metal, textures.glsl:58-63
+        V3 direction = vadd(vreflect(ray.d, normal), vscale(random_in_unit_sphere(u), param));
+        colour = vmul(colour, albedo);
+        ray.o = point; ray.d = direction;
+        return true;
+    }
+    if (kind == 3) {  // glass, textures.glsl:27-56
+        V3 outward_normal, refracted = v3(0.f, 0.f, 0.f);
+        V3 reflected = vreflect(ray.d, normal);
+        float ni_over_nt, reflect_prob, cosine;
+        float dn = vdot(ray.d, normal);
+        if (dn > 0.f) {
+            outward_normal = vneg(normal);
+            ni_over_nt = param;
+            cosine = fsqrt(fsub(1.f, fmul(fmul(param, param), fsub(1.f, fmul(dn, dn)))));
+        } else {
+            outward_normal = normal;
+            ni_over_nt = fdiv(1.f, param);
+            cosine = -dn;
+        }
+        if (modified_refract(ray.d, outward_normal, ni_over_nt, refracted)) reflect_prob = schlick(cosine, param);
+        else reflect_prob = 1.f;
+        ray.o = point;
+        ray.d = (u[0] < reflect_prob) ? reflected : refracted;
+        return true;
+    }
+    return false;
+}
+
+}  // namespace vcrt

@@ -163,6 +163,13 @@ int cudaCommBarrier(void);
    the denominator of the roofline (MEASURED_PEAKS.json carries HBM and bf16 only). */
 int cudaMeasureFp32Peak(OUT double* tflops, OUT double* smClockMHz);
 int cudaGetDeviceInfo(OUT int* smCount, OUT int* maxClockKHz, OUT char* name, IN size_t nameBytes);
+/* CUDA events on the layer's own stream (the stream every kernel of cudaRender is launched on), so a caller
+   can time a region of several calls on the device: record `slot` (0..15) now / milliseconds between two
+   recorded slots (waits for the later one). */
+int cudaStreamMark(IN uint32_t slot);
+int cudaStreamElapsed(IN uint32_t fromSlot, IN uint32_t toSlot, OUT float* milliseconds);
+/* Writes a scratch buffer larger than the L2 on the layer's stream (timing hygiene between timed renders). */
+int cudaFlushL2(void);
 
 #ifdef __cplusplus
 }

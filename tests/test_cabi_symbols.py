@@ -1,0 +1,95 @@
+# SPDX-License-Identifier: WTFPL
+"""The drop-in boundary without a GPU: the C-ABI library loads, exports every function the headers
+declare, keeps its struct layouts, and fails loudly (never falls back to a CPU path) when no device
+is present.  No compute call succeeds here."""
+import ctypes
+import os
+import re
+import subprocess
+
+import pytest
+
+from vulkancomputeraytracing_b200 import cabi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_functions():
+    names = []
+    for header in ("vcrt.h", "SceneGenerator.hpp"):
+        text = open(os.path.join(ROOT, "include", header)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        names += re.findall(r"^\s*(?:const\s+)?[A-Za-z_][\w\s\*]*?\b(\w+)\s*\([^;{]*\)\s*;", text, flags=re.M)
+    return sorted(set(names))
+
+
+def test_every_declared_symbol_is_exported_and_bound(vcrt):
+    names = declared_functions()
+    assert "cudaUploadScene" in names and "cudaRender" in names and "vcrtGenerateScene" in names and len(names) >= 20
+    exported = subprocess.check_output(["nm", "-D", "--defined-only", cabi.LIB_PATH]).decode()
+    for name in names:
+        assert re.search(rf"\sT {name}$", exported, flags=re.M), f"{name} is declared but not exported with C linkage"
+        assert hasattr(vcrt, name)
+    assert sorted(cabi.PROTOTYPES) == names, "cabi.py bindings and the headers disagree"
+
+
+def test_struct_layouts():
+    assert ctypes.sizeof(cabi.VcrtSphere) == 40          # structures.glsl:10-16, 10 floats
+    assert ctypes.sizeof(cabi.VcrtCamera) == 40
+    assert ctypes.sizeof(cabi.VcrtRenderParams) == 56
+    assert cabi.VcrtRenderParams.seed.offset == 16 and cabi.VcrtRenderParams.sampleOffset.offset == 24
+    assert ctypes.sizeof(cabi.VcrtRenderStats) == 8 * 8 + 4 * 8 + 8 * 8 + 6 * 4
+    assert ctypes.sizeof(cabi.VcrtSceneRecipe) == 24
+
+
+def test_defaults_are_the_reference_constants(vcrt):
+    p = cabi.VcrtRenderParams()
+    vcrt.vcrtDefaultRenderParams(ctypes.byref(p))
+    assert (p.width, p.height, p.samplesPerPixel, p.maxDepth) == (1280, 720, 1, 50)    # globals.glsl:12-17
+    c = cabi.VcrtCamera()
+    vcrt.vcrtDefaultCamera(ctypes.byref(c))
+    assert list(c.lookfrom) == [13, 2, 3] and list(c.lookat) == [0, 0, 0] and list(c.vup) == [0, 1, 0] and c.vfov == 20
+
+
+def test_argument_errors_need_no_device(vcrt):
+    assert vcrt.cudaRender(None) == cabi.VCRT_ERROR_INVALID_ARGUMENT
+    assert vcrt.cudaUploadScene(None, 3, None) == cabi.VCRT_ERROR_INVALID_ARGUMENT
+    assert vcrt.cudaDownloadImage(None, 0) == cabi.VCRT_ERROR_INVALID_ARGUMENT
+    assert vcrt.cudaSelectDevice(-1) == cabi.VCRT_ERROR_INVALID_ARGUMENT
+    assert b"null" in vcrt.cudaGetLastErrorString() or b"negative" in vcrt.cudaGetLastErrorString()
+    assert vcrt.cudaDestroyRenderer() == cabi.VCRT_SUCCESS      # tolerates never-created state (Renderer.cpp:716-773)
+
+
+def no_gpu():
+    import torch
+    return not torch.cuda.is_available()
+
+
+@pytest.mark.skipif(not no_gpu(), reason="only meaningful on a machine without a GPU")
+def test_no_device_is_a_loud_error_not_a_cpu_fallback(vcrt):
+    from vulkancomputeraytracing_b200 import host
+    with pytest.raises(cabi.VcrtError) as e:
+        host.upload_scene(host.generate_scene())
+    assert e.value.code == cabi.VCRT_ERROR_NO_DEVICE and "no CPU path" in str(e.value)
+    p = host.render_params(16, 16, 1)
+    assert vcrt.cudaRender(ctypes.byref(p)) == cabi.VCRT_ERROR_NO_DEVICE
+    exe = os.path.join(os.path.dirname(cabi.LIB_PATH), "VulkanComputeRayTracing")
+    run = subprocess.run([exe, "--width", "16", "--height", "16"], capture_output=True)
+    assert run.returncode != 0 and b"Cannot begin rendering operation" in run.stderr
+
+
+def test_product_never_touches_the_oracle():
+    # the oracle is test infrastructure: nothing under the package, include/ or the C-ABI may reference it
+    bad = []
+    for base in ("vulkancomputeraytracing_b200", "include"):
+        for folder, _, files in os.walk(os.path.join(ROOT, base)):
+            if "__pycache__" in folder:
+                continue
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
+                    text = open(os.path.join(folder, f), errors="ignore").read()
+                    if re.search(r"oracle/|liboracle|oracle_harness|import oracle|_ref/", text):
+                        bad.append(os.path.join(folder, f))
+    assert not bad, bad
+    deps = subprocess.check_output(["ldd", cabi.LIB_PATH]).decode()
+    assert "oracle" not in deps and "vcrt_ref" not in deps

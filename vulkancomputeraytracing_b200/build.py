@@ -1,7 +1,12 @@
 # SPDX-License-Identifier: WTFPL
-"""Builds lib/libvcrt.so (CUDA, sm_100a) and the C++ host programs in-tree with nvcc / g++.
+"""Builds the product in-tree with nvcc / g++ (no JIT cache: the .so travels with the repo snapshot).
 
     python -m vulkancomputeraytracing_b200.build [--force]
+
+Outputs (all under vulkancomputeraytracing_b200/lib/, git-ignored):
+    libvcrt.so                 the C ABI of include/vcrt.h + include/SceneGenerator.hpp (CUDA, sm_100a)
+    VulkanComputeRayTracing    the headless host program (Begin / Draw / End over the C ABI)
+    SceneGenerator             prints the scene as GLSL text like the reference's tool
 """
 import os
 import subprocess
@@ -12,11 +17,13 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 HOST = os.path.join(HERE, "host")
 LIB = os.path.join(HERE, "lib")
+INCLUDE = os.path.join(ROOT, "include")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 GXX = "/usr/bin/g++"   # the image's $CXX (/opt/gcc) lacks libgomp.spec; pin the distro compiler
 
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++20",
               "-Xcompiler", "-fPIC,-ffp-contract=off", "-ccbin", GXX]
+GXX_FLAGS = ["-std=c++20", "-O2", "-ffp-contract=off", "-Wall", "-I", INCLUDE]
 
 
 def _newer(target, sources):
@@ -31,25 +38,25 @@ def _run(cmd):
     subprocess.check_call(cmd)
 
 
+def _listing(folder, suffixes):
+    return [os.path.join(folder, f) for f in sorted(os.listdir(folder)) if f.endswith(suffixes)]
+
+
 def build(force=False):
     os.makedirs(LIB, exist_ok=True)
-    cu_sources = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))] + [os.path.join(ROOT, "include", "vcrt.h")]
+    headers = _listing(INCLUDE, (".h", ".hpp"))
     target = os.path.join(LIB, "libvcrt.so")
-    if force or _newer(target, cu_sources):
-        _run([NVCC] + NVCC_FLAGS + ["-shared", "-o", target, os.path.join(CSRC, "vcrt_cabi.cu"), "-ldl"])
-    if os.path.isdir(HOST):
-        host_sources = [os.path.join(HOST, f) for f in sorted(os.listdir(HOST)) if f.endswith(".cpp")]
-        headers = [os.path.join(ROOT, "include", f) for f in sorted(os.listdir(os.path.join(ROOT, "include")))]
-        exe = os.path.join(LIB, "VulkanComputeRayTracing")
-        main_sources = [s for s in host_sources if not s.endswith("SceneGeneratorMain.cpp")]
-        if main_sources and (force or _newer(exe, main_sources + headers + [target])):
-            _run([GXX, "-std=c++20", "-O2", "-ffp-contract=off", "-I", os.path.join(ROOT, "include"), "-o", exe] + main_sources +
-                 ["-L", LIB, "-lvcrt", "-Wl,-rpath,$ORIGIN"])
-        gen = os.path.join(HOST, "SceneGeneratorMain.cpp")
-        gen_exe = os.path.join(LIB, "SceneGenerator")
-        if os.path.exists(gen) and (force or _newer(gen_exe, [gen, os.path.join(HOST, "SceneGenerator.cpp")] + headers)):
-            _run([GXX, "-std=c++20", "-O2", "-ffp-contract=off", "-I", os.path.join(ROOT, "include"), "-o", gen_exe, gen,
-                  os.path.join(HOST, "SceneGenerator.cpp")])
+    scene = os.path.join(HOST, "SceneGenerator.cpp")
+    if force or _newer(target, _listing(CSRC, (".cu", ".cuh")) + headers + [scene]):
+        _run([NVCC] + NVCC_FLAGS + ["-shared", "-o", target, os.path.join(CSRC, "vcrt_cabi.cu"), scene, "-ldl"])
+    exe = os.path.join(LIB, "VulkanComputeRayTracing")
+    main_sources = [os.path.join(HOST, f) for f in ("VulkanComputeRayTracing.cpp", "Renderer.cpp", "Frontend.cpp", "Platform.cpp")]
+    if force or _newer(exe, main_sources + headers + [target]):
+        _run([GXX] + GXX_FLAGS + ["-o", exe] + main_sources + ["-L", LIB, "-lvcrt", "-Wl,-rpath,$ORIGIN"])
+    gen_exe = os.path.join(LIB, "SceneGenerator")
+    gen = os.path.join(HOST, "SceneGeneratorMain.cpp")
+    if force or _newer(gen_exe, [gen, scene] + headers):
+        _run([GXX] + GXX_FLAGS + ["-o", gen_exe, gen, scene])
     return target
 
 

@@ -52,13 +52,21 @@ class VcrtRenderStats(ctypes.Structure):
                 ("traversalUsed", ctypes.c_uint32), ("sampleChunksUsed", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
 
 
+class VcrtSceneRecipe(ctypes.Structure):
+    _fields_ = [("gridHalf", ctypes.c_int32), ("variant", ctypes.c_uint32),
+                ("lambertBelow", ctypes.c_double), ("metalBelow", ctypes.c_double)]
+
+
+VCRT_SCENE_REFERENCE, VCRT_SCENE_STRESS = 0, 1
+
+
 class VcrtError(RuntimeError):
     def __init__(self, code, text):
         super().__init__(f"vcrt error {code}: {text}")
         self.code = code
 
 
-# Every symbol include/vcrt.h declares; tests/test_cabi_symbols.py checks the two lists agree.
+# Every symbol include/vcrt.h and include/SceneGenerator.hpp declare; tests/test_cabi_symbols.py checks the lists agree.
 PROTOTYPES = {
     "vcrtDefaultRenderParams": (None, [ctypes.POINTER(VcrtRenderParams)]),
     "vcrtDefaultCamera": (None, [ctypes.POINTER(VcrtCamera)]),
@@ -79,6 +87,14 @@ PROTOTYPES = {
     "cudaCommBarrier": (ctypes.c_int, []),
     "cudaMeasureFp32Peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
     "cudaGetDeviceInfo": (ctypes.c_int, [ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), ctypes.c_char_p, ctypes.c_size_t]),
+    "cudaStreamMark": (ctypes.c_int, [ctypes.c_uint32]),
+    "cudaStreamElapsed": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(ctypes.c_float)]),
+    "cudaFlushL2": (ctypes.c_int, []),
+    "vcrtDefaultSceneRecipe": (None, [ctypes.POINTER(VcrtSceneRecipe)]),
+    "vcrtSceneCapacity": (ctypes.c_uint32, [ctypes.POINTER(VcrtSceneRecipe)]),
+    "vcrtGenerateScene": (ctypes.c_int32, [ctypes.POINTER(VcrtSceneRecipe), ctypes.POINTER(VcrtSphere), ctypes.c_uint32]),
+    "vcrtSceneToGlsl": (ctypes.c_size_t, [ctypes.POINTER(VcrtSphere), ctypes.c_uint32, ctypes.c_char_p, ctypes.c_size_t]),
+    "vcrtSceneFromGlsl": (ctypes.c_int32, [ctypes.c_char_p, ctypes.POINTER(VcrtSphere), ctypes.c_uint32]),
 }
 
 _lib = None

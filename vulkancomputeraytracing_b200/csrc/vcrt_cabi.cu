@@ -308,6 +308,32 @@ extern "C" int cudaMeasureFp32Peak(OUT double* tflops, OUT double* smClockMHz) {
     return VCRT_SUCCESS;
 }
 
+static cudaEvent_t cudaComputeMarks[16];
+static bool cudaComputeMarkReady[16];
+static void* cudaComputeFlushScratch = nullptr;
+static const size_t kFlushBytes = 256u << 20;   // 2x the 126 MB L2
+
+extern "C" int cudaStreamMark(IN uint32_t slot) {
+    if (slot >= 16) return fail(VCRT_ERROR_INVALID_ARGUMENT, "mark slot out of range%s", "");
+    int rc = ensureDevice(); if (rc) return rc;
+    if (!cudaComputeMarkReady[slot]) { CUDA_TRY(cudaEventCreate(&cudaComputeMarks[slot])); cudaComputeMarkReady[slot] = true; }
+    CUDA_TRY(cudaEventRecord(cudaComputeMarks[slot], cudaComputeStream));
+    return VCRT_SUCCESS;
+}
+extern "C" int cudaStreamElapsed(IN uint32_t fromSlot, IN uint32_t toSlot, OUT float* milliseconds) {
+    if (fromSlot >= 16 || toSlot >= 16 || !milliseconds) return fail(VCRT_ERROR_INVALID_ARGUMENT, "bad mark arguments%s", "");
+    if (!cudaComputeMarkReady[fromSlot] || !cudaComputeMarkReady[toSlot]) return fail(VCRT_ERROR_NOT_READY, "mark never recorded%s", "");
+    CUDA_TRY(cudaEventSynchronize(cudaComputeMarks[toSlot]));
+    CUDA_TRY(cudaEventElapsedTime(milliseconds, cudaComputeMarks[fromSlot], cudaComputeMarks[toSlot]));
+    return VCRT_SUCCESS;
+}
+extern "C" int cudaFlushL2(void) {
+    int rc = ensureDevice(); if (rc) return rc;
+    if (!cudaComputeFlushScratch) CUDA_TRY(cudaMalloc(&cudaComputeFlushScratch, kFlushBytes));
+    CUDA_TRY(cudaMemsetAsync(cudaComputeFlushScratch, 0x5a, kFlushBytes, cudaComputeStream));
+    return VCRT_SUCCESS;
+}
+
 // ------------------------------------------------------------------ buffers
 static int ensureImageBuffers(uint32_t width, uint32_t height, uint32_t chunks) {
     const size_t pixels = (size_t)width * height;
@@ -575,15 +601,16 @@ extern "C" int cudaDestroyRenderer(void) {
         cudaSetDevice(cudaComputeDevice);
         if (cudaComputeStream) cudaStreamSynchronize(cudaComputeStream);
         void* buffers[] = {cudaComputeSceneBlob, cudaComputeSumPlanes, cudaComputeAccumulated, cudaComputeReduced, cudaComputeFixedSums, cudaComputeFixedReduced,
-                           cudaComputeResultImage, cudaComputeCounters, cudaComputeWorkCounter, cudaComputeCommScratch};
+                           cudaComputeResultImage, cudaComputeCounters, cudaComputeWorkCounter, cudaComputeCommScratch, cudaComputeFlushScratch};
         for (void* b : buffers) if (b) cudaFree(b);
+        for (int i = 0; i < 16; i++) if (cudaComputeMarkReady[i]) { cudaEventDestroy(cudaComputeMarks[i]); cudaComputeMarkReady[i] = false; }
         for (int i = 0; i < 4; i++) if (cudaComputeEvents[i]) cudaEventDestroy(cudaComputeEvents[i]);
         if (cudaComputeStream) cudaStreamDestroy(cudaComputeStream);
     }
     cudaComputeSceneBlob = nullptr; cudaComputeSumPlanes = nullptr; cudaComputeSumPlanesBytes = 0;
     cudaComputeAccumulated = cudaComputeReduced = cudaComputeResultImage = nullptr;
     cudaComputeFixedSums = cudaComputeFixedReduced = nullptr;
-    cudaComputeCounters = nullptr; cudaComputeWorkCounter = nullptr; cudaComputeCommScratch = nullptr;
+    cudaComputeCounters = nullptr; cudaComputeWorkCounter = nullptr; cudaComputeCommScratch = nullptr; cudaComputeFlushScratch = nullptr;
     cudaComputeStream = nullptr; for (int i = 0; i < 4; i++) cudaComputeEvents[i] = nullptr;
     cudaComputeImageWidth = cudaComputeImageHeight = 0; cudaComputeAccumulatedSamples = 0;
     cudaComputeImageValid = false; cudaComputeSceneReady = false; cudaComputeDeviceReady = false;

@@ -1,17 +1,16 @@
-# dev script: one render through the C ABI (for ncu). usage: prof_run.py W H spp traversal [chunks]
-import ctypes, sys, numpy as np
+# dev script: renders through the C ABI (for ncu / quick timing). usage: prof_run.py W H spp traversal [chunks] [scene] [reps]
+import sys
 sys.path.insert(0, '.')
-from vulkancomputeraytracing_b200 import cabi
-L = cabi.load(); vp = ctypes.c_void_p
-O = ctypes.CDLL('oracle/_build/liboracle.so')
-O.oracle_generate_scene.argtypes=[ctypes.c_int, ctypes.c_double, ctypes.c_double, vp, ctypes.c_int]
-g = np.zeros((600,10), np.float32); n = O.oracle_generate_scene(11, 0.8, 0.95, g.ctypes.data_as(vp), 600); w = np.ascontiguousarray(g[:n])
-c = cabi.VcrtCamera(); L.vcrtDefaultCamera(ctypes.byref(c))
-cabi.check(L.cudaUploadScene(w.ctypes.data_as(ctypes.POINTER(cabi.VcrtSphere)), n, ctypes.byref(c)))
-W,H,spp,trav = map(int, sys.argv[1:5]); chunks = int(sys.argv[5]) if len(sys.argv) > 5 else 0
-p = cabi.VcrtRenderParams(); L.vcrtDefaultRenderParams(ctypes.byref(p))
-p.width, p.height, p.samplesPerPixel, p.traversal, p.sampleChunks = W,H,spp,trav,chunks
-for i in range(2):
-    cabi.check(L.cudaRender(ctypes.byref(p)))
-    st = cabi.VcrtRenderStats(); L.cudaGetRenderStats(ctypes.byref(st))
-    print(f'kernel {st.renderKernelMs:.2f} ms  {st.rays*n/st.renderKernelMs/1e9:.3f} Ttests/s  chunks {st.sampleChunksUsed}')
+from vulkancomputeraytracing_b200 import host
+W, H, spp, trav = map(int, sys.argv[1:5]); chunks = int(sys.argv[5]) if len(sys.argv) > 5 else 0
+kind = sys.argv[6] if len(sys.argv) > 6 else "reference"; reps = int(sys.argv[7]) if len(sys.argv) > 7 else 2; shape = int(sys.argv[8]) if len(sys.argv) > 8 else 0
+scene = host.stress_scene() if kind == "stress" else host.generate_scene(11 if kind == "reference" else int(kind))
+n = scene.shape[0]
+host.upload_scene(scene)
+for i in range(reps):
+    _, st = host.render(W, H, spp, traversal=trav, sample_chunks=chunks, download=False, shape=shape)
+    print(f'{W}x{H}x{spp} trav={st.traversalUsed} n={n}: kernel {st.renderKernelMs:.2f} ms total {st.totalMs:.2f} ms  {st.samples/st.renderKernelMs/1e3:.1f} Msamples/s  '
+          f'{st.rays/st.renderKernelMs/1e3:.1f} Mrays/s  {st.rays*n/st.renderKernelMs/1e9:.3f} Ttests/s  alg {st.rays*n*17/st.renderKernelMs/1e9:.1f} TF  '
+          f'rays/sample {st.rays/st.samples:.4f} cand/ray {st.candidates/max(1,st.rays):.2f} ovf {st.listOverflows} nodes/ray {st.nodeVisits/max(1,st.rays):.1f}', flush=True)
+tf, mhz = host.fp32_peak(); print(f'fp32 peak {tf:.1f} TF at {mhz:.0f} MHz')
+host.destroy()

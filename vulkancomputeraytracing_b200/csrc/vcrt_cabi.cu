@@ -506,7 +506,12 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         CUDA_TRY(cudaGetLastError());
         launches++;
     } else {
-        if (fixedMode) rc = wide ? launchScan<512, 2, 12, true>(args, &launches) : launchScan<256, 2, 12, true>(args, &launches);
+        // reserved[1]: experiment switch for the CTA shape (0 = default)
+        const uint32_t shape = p->reserved[1];
+        if (shape == 2 && fixedMode && scanFits(1024, 1, 12)) rc = launchScan<1024, 1, 12, true>(args, &launches);
+        else if (shape == 3 && fixedMode && scanFits(768, 1, 12)) rc = launchScan<768, 1, 12, true>(args, &launches);
+        else if (shape == 4 && fixedMode && scanFits(640, 1, 12)) rc = launchScan<640, 1, 12, true>(args, &launches);
+        else if (fixedMode) rc = wide ? launchScan<512, 2, 12, true>(args, &launches) : launchScan<256, 2, 12, true>(args, &launches);
         else rc = wide ? launchScan<512, 2, 12, false>(args, &launches) : launchScan<256, 2, 12, false>(args, &launches);
         if (rc) return rc;
     }

@@ -185,7 +185,10 @@ def run_b200(args):
     scene = build_scene(host, scene_kind)
     count = scene.shape[0]
     offset, my_spp = sharding.shard_samples(spp, world, rank)
-    traversal = {"auto": 0, "brute": 1, "lbvh": 2, "simple": 3}[args.traversal]
+    # headline traversal: north_star's linear scan (every ray tests every sphere; FP32-FMA roofline) for the
+    # 485-sphere workloads, the GPU-built LBVH for the 10k / 100k scenes that cannot be scanned
+    default_traversal = "lbvh" if name.startswith("c4") else "brute"
+    traversal = {"auto": 0, "brute": 1, "lbvh": 2, "simple": 3}[args.traversal or default_traversal]
     host.upload_scene(scene)
     params = host.render_params(w, h, my_spp, depth=depth, seed=args.seed, sample_offset=offset, traversal=traversal, total_samples=spp)
     image = np.empty((h, w, 4), np.float32)
@@ -250,6 +253,20 @@ def run_b200(args):
     for _ in range(1):
         step_e2e()
     e_ms, e_wall, *_ = timed(step_e2e, args.steps)
+    # the same workload through the LBVH (optional in north_star, but faster even at 485 spheres): reported beside the headline
+    lbvh = None
+    if traversal == 1:
+        params.traversal = 2
+        for _ in range(2):
+            step_resident()
+        l_ms, _, l_kernel, l_rays, _, _ = timed(step_resident, args.steps)
+        l_ms_max = max_over_ranks(l_ms); l_rays_total = sum_over_ranks(l_rays)
+        st_l = host.stats()
+        lbvh = {"value": w * h * spp * args.steps / (l_ms_max * 1e-3), "unit": "samples/s", "ms_per_step": l_ms_max / args.steps,
+                "mrays_per_sec": l_rays_total / (l_ms_max * 1e-3) * 1e-6, "node_visits_per_ray": st_l.nodeVisits / max(1, st_l.rays),
+                "sphere_tests_per_ray": st_l.sphereTests / max(1, st_l.rays)}
+        params.traversal = traversal
+        step_resident()   # leave the layer's stats / image on the headline traversal
     # e2e is wall-clock around the public calls (uploads, render, read-back), max over ranks
     e_wall_max = max_over_ranks(e_wall)
 
@@ -287,6 +304,16 @@ def run_b200(args):
                          "filter_candidates_per_ray": cand / rays if rays else None},
             "clocks": clocks, "gpu": gpu_name,
         }
+        if lbvh is not None:
+            lbvh["speedup_vs_headline"] = lbvh["value"] / value
+            line["lbvh_same_workload"] = lbvh
+        if host.stats().traversalUsed == 2:
+            st = host.stats()
+            line["roofline"].update({"bound": "latency (divergent tree traversal; FP32 flop shown for scale)",
+                                     "algorithmic": "node visits x 2 boxes x 24 flop + leaf sphere tests x 17 flop, from the in-kernel counters",
+                                     "achieved": (st.nodeVisits * 48 + st.sphereTests * 17) / (st.renderKernelMs * 1e-3) * 1e-12,
+                                     "node_visits_per_ray": st.nodeVisits / max(1, st.rays), "sphere_tests_per_ray": st.sphereTests / max(1, st.rays)})
+            line["roofline"]["frac"] = line["roofline"]["achieved"] / peak_tf
         if not args.no_cpu and world >= 1:
             line["cpu_baseline"] = cpu_baseline(w, h, spp, depth, scene_kind)
         print(json.dumps(line), flush=True)
@@ -304,7 +331,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
-    ap.add_argument("--traversal", default="auto", choices=["auto", "brute", "lbvh", "simple"])
+    ap.add_argument("--traversal", default=None, choices=["auto", "brute", "lbvh", "simple"])
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

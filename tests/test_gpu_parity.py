@@ -217,3 +217,45 @@ def test_host_program_end_to_end(tmp_path, oracle):
     assert np.abs(pfm - cpu[..., :3]).max() <= 2.0 ** -22       # 2 progressive frames of 2 spp == 4 spp
     with open(prefix + ".ppm", "rb") as f:
         assert f.readline() == b"P6\n"
+
+
+@pytest.mark.parametrize("grid", [50, 158])
+def test_lbvh_bit_exact_on_scaled_scenes(oracle, vcrt, grid):
+    # BASELINE.json configs[3]: 10 k (grid 50) and 100 k (grid 158) spheres through the GPU-built LBVH
+    scene = host.generate_scene(grid)
+    assert scene.shape[0] == {50: 10003, 158: 99857}[grid]
+    host.upload_scene(scene)
+    try:
+        w, h, spp = (96, 54, 2) if grid == 50 else (64, 36, 1)
+        cpu, cst = oracle.render(scene, w, h, spp)
+        gpu, st = host.render(w, h, spp, traversal=LBVH, sample_chunks=1)
+        assert_same(gpu, st, cpu, cst)
+        assert st.nodeVisits > 0 and st.sphereTests < st.rays * scene.shape[0] // 50      # the tree really prunes
+        auto, sa = host.render(w, h, spp, sample_chunks=1)                                 # AUTO picks the LBVH at this size
+        assert sa.traversalUsed == LBVH and np.array_equal(auto, gpu)
+        # a larger frame against the on-device exhaustive kernel (every sphere tested exactly for every ray)
+        simple, ss = host.render(320, 180, 1, traversal=SIMPLE, sample_chunks=1)
+        tree, stt = host.render(320, 180, 1, traversal=LBVH, sample_chunks=1)
+        assert ss.rays == stt.rays and np.array_equal(simple, tree)
+        fixed, _ = host.render(320, 180, 1, traversal=LBVH)                                # default fixed-point sums
+        assert np.abs(fixed - tree).max() <= 2.0 ** -22
+    finally:
+        host.destroy()
+
+
+def test_lbvh_duplicates_and_coincident_centres(oracle, vcrt):
+    # identical spheres (exact ties: the lower index must win, as in the reference's in-order scan), concentric shells
+    rng = np.random.default_rng(5)
+    base = random_scene(rng, 40)
+    scene = np.concatenate([base, base[::-1], base[:10]])             # every sphere at least twice, different materials order
+    scene[80:, 7] = 2; scene[80:, 8] = 0.5                            # the third copies are metal: a wrong tie-break changes the image
+    scene = np.concatenate([scene, [[0, 0, 0, r, .9, .9, .9, 3, 1.5, 0] for r in (0.5, 1.0, 1.5, 2.0)]]).astype(np.float32)
+    cam = cabi.VcrtCamera((ctypes.c_float * 3)(0, 1, 14), (ctypes.c_float * 3)(0, 0, 0), (ctypes.c_float * 3)(0, 1, 0), 50.0)
+    host.upload_scene(scene, cam)
+    try:
+        cpu, cst = oracle.render(scene, 96, 64, 2, depth=12, camera=host.camera_array(cam))
+        for traversal in (LBVH, BRUTE, SIMPLE):
+            gpu, st = host.render(96, 64, 2, depth=12, traversal=traversal, sample_chunks=1)
+            assert_same(gpu, st, cpu, cst)
+    finally:
+        host.destroy()

@@ -9,6 +9,9 @@
 #include "../../include/vcrt.h"
 #include "vcrt_kernel_simple.cuh"
 #include "vcrt_kernel_scan.cuh"
+#include "vcrt_kernel_lbvh.cuh"
+
+#include <cub/device/device_radix_sort.cuh>
 
 #include <cuda_runtime.h>
 #include <dlfcn.h>
@@ -30,6 +33,13 @@ static cudaEvent_t cudaComputeEvents[4] = {nullptr, nullptr, nullptr, nullptr};
 static unsigned char* cudaComputeSceneBlob = nullptr;   // device copy of the SoA blob
 static SceneBlob cudaComputeSceneHeader;
 static bool cudaComputeSceneReady = false;
+struct SceneExtent { float centreMin[3], centreMax[3], radiusMin, radiusMax; };
+static SceneExtent cudaComputeSceneExtent;
+// LBVH over the scan spheres (device indices [0, scanCount)), built on first use after an upload
+static bool cudaComputeBvhReady = false;
+static void* cudaComputeBvhArena = nullptr;
+static size_t cudaComputeBvhArenaBytes = 0;
+static BvhScene cudaComputeBvhScene;
 static VcrtCamera cudaComputeCamera;
 
 static float4* cudaComputeSumPlanes = nullptr;          // [chunks][W*H] partial sums of the last render
@@ -156,13 +166,26 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
     hdr.offShape = hdr.offHot + scanPad * 16u;
     hdr.offSurf = hdr.offShape + count * 16u;
     hdr.offKind = hdr.offSurf + count * 16u;
-    hdr.bytes = (hdr.offKind + count * 4u + 15u) & ~15u;
+    hdr.offOrig = (hdr.offKind + count * 4u + 15u) & ~15u;
+    hdr.bytes = (hdr.offOrig + count * 4u + 15u) & ~15u;
     unsigned char* host = (unsigned char*)calloc(1, hdr.bytes);
     if (!host) { delete[] order; return fail(VCRT_ERROR_OUT_OF_MEMORY, "scene blob%s", ""); }
     float4* hot = (float4*)(host + hdr.offHot); float4* shape = (float4*)(host + hdr.offShape);
     float4* surf = (float4*)(host + hdr.offSurf); int* kind = (int*)(host + hdr.offKind);
+    uint32_t* orig = (uint32_t*)(host + hdr.offOrig);
+    SceneExtent extent; memset(&extent, 0, sizeof extent);
     for (uint32_t j = 0; j < count; j++) {
         const VcrtSphere& s = spheres[order[j]];
+        orig[j] = order[j];
+        if (j < scanCount) {   // what the LBVH needs to know about the spheres it will hold
+            const float r = fabsf(s.radius);
+            for (int k = 0; k < 3; k++) {
+                extent.centreMin[k] = j ? fminf(extent.centreMin[k], s.center[k]) : s.center[k];
+                extent.centreMax[k] = j ? fmaxf(extent.centreMax[k], s.center[k]) : s.center[k];
+            }
+            extent.radiusMin = j ? fminf(extent.radiusMin, r) : r;
+            extent.radiusMax = j ? fmaxf(extent.radiusMax, r) : r;
+        }
         shape[j] = make_float4(s.center[0], s.center[1], s.center[2], s.radius);
         surf[j] = make_float4(s.colour[0], s.colour[1], s.colour[2], s.texture[1]);
         kind[j] = (int)s.texture[0];   // switch(int(record.texture.x)), textures.glsl:66
@@ -187,6 +210,8 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
     free(host);
     if (e != cudaSuccess) return fail(VCRT_ERROR_CUDA, "scene upload: %s", cudaGetErrorString(e));
     cudaComputeSceneHeader = hdr;
+    cudaComputeSceneExtent = extent;
+    cudaComputeBvhReady = false;
     cudaComputeCamera = *camera;
     cudaComputeSceneReady = true;
     cudaComputeImageValid = false;
@@ -304,7 +329,9 @@ extern "C" int cudaMeasureFp32Peak(OUT double* tflops, OUT double* smClockMHz) {
     double flop = (double)threads * blocks * iters * 64.0 * 2.0;
     if (tflops) *tflops = flop / (best * 1e-3) * 1e-12;
     // one block's loop = 4 resident blocks/SM x 16 warps sharing 4 schedulers: cycles are wall cycles of that SM
-    if (smClockMHz) *smClockMHz = (double)hostCycles / (best * 1e-3) * 1e-6;
+    (void)hostCycles;
+    // the SM clock this rate corresponds to if every FP32 lane retired one FMA per cycle (128 lanes per SM)
+    if (smClockMHz && tflops) *smClockMHz = *tflops * 1e12 / (2.0 * 128.0 * cudaComputeSmCount) * 1e-6;
     return VCRT_SUCCESS;
 }
 
@@ -425,6 +452,82 @@ extern "C" int cudaCommMaxFloat(IN float value, OUT float* maxValue) {
 }
 extern "C" int cudaCommBarrier(void) { float v = 0.f, m; return cudaCommMaxFloat(v, &m); }
 
+// ------------------------------------------------------------------ LBVH build (vcrt_lbvh.cuh)
+static size_t alignUp(size_t v) { return (v + 255) & ~(size_t)255; }
+static int ensureBvh(void) {
+    if (cudaComputeBvhReady) return VCRT_SUCCESS;
+    const SceneBlob& hdr = cudaComputeSceneHeader;
+    const uint32_t n = hdr.scanCount;
+    BvhScene& bs = cudaComputeBvhScene; memset(&bs, 0, sizeof bs);
+    bs.shape = (const float4*)(cudaComputeSceneBlob + hdr.offShape); bs.surf = (const float4*)(cudaComputeSceneBlob + hdr.offSurf);
+    bs.kind = (const int*)(cudaComputeSceneBlob + hdr.offKind); bs.origIndex = (const uint32_t*)(cudaComputeSceneBlob + hdr.offOrig);
+    bs.treeCount = n; bs.count = hdr.count;
+    const SceneExtent& e = cudaComputeSceneExtent;
+    bs.centreMin = make_float3(e.centreMin[0], e.centreMin[1], e.centreMin[2]); bs.centreMax = make_float3(e.centreMax[0], e.centreMax[1], e.centreMax[2]);
+    bs.radiusMin = e.radiusMin; bs.radiusMax = e.radiusMax;
+    if (n == 0) { cudaComputeBvhReady = true; return VCRT_SUCCESS; }
+    size_t sortBytes = 0;
+    CUDA_TRY(cub::DeviceRadixSort::SortKeys(nullptr, sortBytes, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)n, 0, 64, cudaComputeStream));
+    const size_t nodes = n > 1 ? n - 1 : 1;
+    size_t off = 0;
+    const size_t offKeysIn = off; off += alignUp(sizeof(unsigned long long) * n);
+    const size_t offKeys = off; off += alignUp(sizeof(unsigned long long) * n);
+    const size_t offLeafShape = off; off += alignUp(sizeof(float4) * n);
+    const size_t offLeafOrig = off; off += alignUp(sizeof(uint32_t) * n);
+    const size_t offLeafDevice = off; off += alignUp(sizeof(uint32_t) * n);
+    const size_t offNodes = off; off += alignUp(sizeof(BvhNode) * nodes);
+    const size_t offParent = off; off += alignUp(sizeof(int) * (2 * (size_t)n));
+    const size_t offBounds = off; off += alignUp(sizeof(float) * 6 * (2 * (size_t)n));
+    const size_t offArrivals = off; off += alignUp(sizeof(unsigned int) * nodes);
+    const size_t offSort = off; off += alignUp(sortBytes);
+    if (off > cudaComputeBvhArenaBytes) {
+        if (cudaComputeBvhArena) cudaFree(cudaComputeBvhArena);
+        cudaComputeBvhArena = nullptr; cudaComputeBvhArenaBytes = 0;
+        CUDA_TRY(cudaMalloc(&cudaComputeBvhArena, off));
+        cudaComputeBvhArenaBytes = off;
+    }
+    unsigned char* arena = (unsigned char*)cudaComputeBvhArena;
+    BvhBuildArgs g; memset(&g, 0, sizeof g);
+    g.shape = bs.shape; g.origIndex = bs.origIndex; g.count = n;
+    g.boxMin = bs.centreMin;
+    auto inv = [](float lo, float hi) { return hi > lo ? 1.0f / (hi - lo) : 0.0f; };
+    g.boxInvExtent = make_float3(inv(e.centreMin[0], e.centreMax[0]), inv(e.centreMin[1], e.centreMax[1]), inv(e.centreMin[2], e.centreMax[2]));
+    unsigned long long* keysIn = (unsigned long long*)(arena + offKeysIn);
+    g.keys = keysIn;
+    g.leafShape = (float4*)(arena + offLeafShape); g.leafOrig = (uint32_t*)(arena + offLeafOrig); g.leafDevice = (uint32_t*)(arena + offLeafDevice);
+    g.nodes = (BvhNode*)(arena + offNodes); g.parent = (int*)(arena + offParent); g.bounds = (float*)(arena + offBounds);
+    g.arrivals = (unsigned int*)(arena + offArrivals);
+    const unsigned int blocks = (n + 255) / 256;
+    lbvh_keys_kernel<<<blocks, 256, 0, cudaComputeStream>>>(g);
+    CUDA_TRY(cub::DeviceRadixSort::SortKeys(arena + offSort, sortBytes, keysIn, (unsigned long long*)(arena + offKeys), (int)n, 0, 64, cudaComputeStream));
+    g.keys = (unsigned long long*)(arena + offKeys);
+    CUDA_TRY(cudaMemsetAsync(g.arrivals, 0, sizeof(unsigned int) * nodes, cudaComputeStream));
+    lbvh_leaves_kernel<<<blocks, 256, 0, cudaComputeStream>>>(g);
+    if (n > 1) {
+        lbvh_hierarchy_kernel<<<blocks, 256, 0, cudaComputeStream>>>(g);
+        lbvh_refit_kernel<<<blocks, 256, 0, cudaComputeStream>>>(g);
+    }
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(cudaComputeStream));
+    bs.nodes = g.nodes; bs.leafShape = g.leafShape; bs.leafOrig = g.leafOrig; bs.leafDevice = g.leafDevice;
+    cudaComputeBvhReady = true;
+    return VCRT_SUCCESS;
+}
+
+template <bool FIXED>
+static int launchLbvh(const RenderArgs& args, uint32_t* launches) {
+    auto kernel = render_lbvh_kernel<FIXED>;
+    int perSm = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, 256, 0));
+    if (perSm < 1) perSm = 1;
+    const unsigned int zero = 0;
+    CUDA_TRY(cudaMemcpyAsync(cudaComputeWorkCounter, &zero, sizeof zero, cudaMemcpyHostToDevice, cudaComputeStream));
+    kernel<<<(unsigned int)(cudaComputeSmCount * perSm), 256, 0, cudaComputeStream>>>(cudaComputeBvhScene, args);
+    CUDA_TRY(cudaGetLastError());
+    *launches += 1;
+    return VCRT_SUCCESS;
+}
+
 // ------------------------------------------------------------------ render dispatch
 template <int THREADS, int PAIRS, int CAP, bool FIXED>
 static int launchScan(const RenderArgs& args, uint32_t* launches) {
@@ -442,6 +545,7 @@ static int launchScan(const RenderArgs& args, uint32_t* launches) {
 }
 
 static const size_t kSmemBudget = 227 * 1024;
+static const uint32_t kBruteForceLimit = 1024;   // spheres; above this the LBVH is faster (measured)
 static bool scanFits(int threads, int pairs, int cap) {
     size_t state = (size_t)SF_COUNT * 2 * pairs * threads * 4, lists = (size_t)(cap + 2) * 2 * pairs * threads * 2;
     return 16 + (size_t)cudaComputeSceneHeader.bytes + state + lists <= kSmemBudget && cudaComputeSceneHeader.scanPad < 65536u;
@@ -455,8 +559,9 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     if (!cudaComputeSceneReady) return fail(VCRT_ERROR_NOT_READY, "cudaRender before cudaUploadScene%s", "");
 
     uint32_t traversal = p->traversal;
-    if (traversal == VCRT_TRAVERSAL_AUTO) traversal = scanFits(256, 2, 12) ? VCRT_TRAVERSAL_BRUTE : VCRT_TRAVERSAL_SIMPLE;
-    if (traversal == VCRT_TRAVERSAL_LBVH) return fail(VCRT_ERROR_UNSUPPORTED, "LBVH traversal is not built yet%s", "");
+    // AUTO: brute force (the reference's own algorithm) while the scene is small enough for it to win, else the LBVH
+    if (traversal == VCRT_TRAVERSAL_AUTO)
+        traversal = (scanFits(256, 2, 12) && cudaComputeSceneHeader.count <= kBruteForceLimit) ? VCRT_TRAVERSAL_BRUTE : VCRT_TRAVERSAL_LBVH;
     if (traversal == VCRT_TRAVERSAL_BRUTE && !scanFits(256, 2, 12))
         return fail(VCRT_ERROR_UNSUPPORTED, "scene does not fit shared memory for VCRT_TRAVERSAL_BRUTE%s", "");
     if (traversal > VCRT_TRAVERSAL_SIMPLE) return fail(VCRT_ERROR_INVALID_ARGUMENT, "unknown traversal%s", "");
@@ -468,12 +573,13 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     // schedule or the GPU count.  sampleChunks >= 1: float sums in strict sample order per chunk (1 = the oracle's order).
     uint32_t chunks = 1;
     bool fixedMode = false;
-    if (traversal == VCRT_TRAVERSAL_BRUTE) {
+    if (traversal == VCRT_TRAVERSAL_BRUTE || traversal == VCRT_TRAVERSAL_LBVH) {
         chunks = p->sampleChunks;
         fixedMode = chunks == 0;
         if (chunks > p->samplesPerPixel) chunks = p->samplesPerPixel;
         if (chunks < 1u) chunks = 1u;
     }
+    if (traversal == VCRT_TRAVERSAL_LBVH) { rc = ensureBvh(); if (rc) return rc; }
     const uint32_t samplesPerItem = p->reserved[0] ? p->reserved[0] : 1u;   // measured: 1 is fastest (keeps the lanes of a warp on neighbouring pixels)
     rc = ensureImageBuffers(p->width, p->height, chunks); if (rc) return rc;
     const bool keep = (p->flags & VCRT_FLAG_ACCUMULATE) && cudaComputeAccumulatedSamples > 0;
@@ -505,6 +611,9 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         render_simple_kernel<<<grid, 128, 0, cudaComputeStream>>>(scene, args);
         CUDA_TRY(cudaGetLastError());
         launches++;
+    } else if (traversal == VCRT_TRAVERSAL_LBVH) {
+        rc = fixedMode ? launchLbvh<true>(args, &launches) : launchLbvh<false>(args, &launches);
+        if (rc) return rc;
     } else {
         // reserved[1]: experiment switch for the CTA shape (0 = default)
         const uint32_t shape = p->reserved[1];
@@ -558,7 +667,7 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     st.samples = (uint64_t)pixels * p->samplesPerPixel;
     st.rays = ctr[CTR_RAYS]; st.depthExhausted = ctr[CTR_EXHAUSTED]; st.badMaterial = ctr[CTR_BAD_MATERIAL];
     st.candidates = ctr[CTR_CANDIDATES]; st.listOverflows = ctr[CTR_OVERFLOWS];
-    st.sphereTests = st.rays * cudaComputeSceneHeader.count; st.nodeVisits = ctr[CTR_NODES];
+    st.sphereTests = traversal == VCRT_TRAVERSAL_LBVH ? ctr[CTR_TESTS] : st.rays * cudaComputeSceneHeader.count; st.nodeVisits = ctr[CTR_NODES];
     for (int i = 0; i < 4; i++) st.hitsByMaterial[i] = ctr[CTR_HITS0 + i];
     for (int i = 0; i < 8; i++) st.pathLength[i] = ctr[CTR_PATH0 + i];
     CUDA_TRY(cudaEventElapsedTime(&st.renderKernelMs, cudaComputeEvents[1], cudaComputeEvents[2]));
@@ -606,7 +715,7 @@ extern "C" int cudaDestroyRenderer(void) {
         cudaSetDevice(cudaComputeDevice);
         if (cudaComputeStream) cudaStreamSynchronize(cudaComputeStream);
         void* buffers[] = {cudaComputeSceneBlob, cudaComputeSumPlanes, cudaComputeAccumulated, cudaComputeReduced, cudaComputeFixedSums, cudaComputeFixedReduced,
-                           cudaComputeResultImage, cudaComputeCounters, cudaComputeWorkCounter, cudaComputeCommScratch, cudaComputeFlushScratch};
+                           cudaComputeResultImage, cudaComputeCounters, cudaComputeWorkCounter, cudaComputeCommScratch, cudaComputeFlushScratch, cudaComputeBvhArena};
         for (void* b : buffers) if (b) cudaFree(b);
         for (int i = 0; i < 16; i++) if (cudaComputeMarkReady[i]) { cudaEventDestroy(cudaComputeMarks[i]); cudaComputeMarkReady[i] = false; }
         for (int i = 0; i < 4; i++) if (cudaComputeEvents[i]) cudaEventDestroy(cudaComputeEvents[i]);
@@ -616,6 +725,8 @@ extern "C" int cudaDestroyRenderer(void) {
     cudaComputeAccumulated = cudaComputeReduced = cudaComputeResultImage = nullptr;
     cudaComputeFixedSums = cudaComputeFixedReduced = nullptr;
     cudaComputeCounters = nullptr; cudaComputeWorkCounter = nullptr; cudaComputeCommScratch = nullptr; cudaComputeFlushScratch = nullptr;
+    cudaComputeBvhArena = nullptr; cudaComputeBvhArenaBytes = 0; cudaComputeBvhReady = false;
+    cudaComputeBvhArena = nullptr; cudaComputeBvhArenaBytes = 0; cudaComputeBvhReady = false;
     cudaComputeStream = nullptr; for (int i = 0; i < 4; i++) cudaComputeEvents[i] = nullptr;
     cudaComputeImageWidth = cudaComputeImageHeight = 0; cudaComputeAccumulatedSamples = 0;
     cudaComputeImageValid = false; cudaComputeSceneReady = false; cudaComputeDeviceReady = false;

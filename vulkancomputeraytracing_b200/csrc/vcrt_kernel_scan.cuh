@@ -63,7 +63,7 @@ VCRT_DEV void mbar_wait(uint64_t* bar, uint32_t parity) {
 struct SceneBlob {
     uint32_t count, scanCount, scanPad, alwaysCount;
     uint32_t offHot, offShape, offSurf, offKind;  // byte offsets from the blob start
-    uint32_t bytes, pad[3];
+    uint32_t bytes, offOrig, pad[2];   // offOrig: uint32 per device index = index in the caller's array
 };
 
 // Per-slot filter state derived from the ray (o, d):

@@ -106,16 +106,17 @@ def run_reference(args):
     def render(s):
         t = time.perf_counter()
         if ref is not None:
-            _, st = ref.render(w, h, s, depth)
+            _, st = ref.render(w, h, s, depth, threads=cores)
         else:
-            _, st = orc.render(scene, w, h, s, depth=depth, rng=oh.RNG_HASH)
+            _, st = orc.render(scene, w, h, s, depth=depth, rng=oh.RNG_HASH, threads=cores)
         return time.perf_counter() - t, st
     cw, ch = max(1, w // 8), max(1, h // 8)
+    render(1) if w * h <= 100000 else None   # thread pool start-up stays out of the calibration
     t = time.perf_counter()
     if ref is not None:
-        ref.render(cw, ch, 2, depth)
+        ref.render(cw, ch, 2, depth, threads=cores)
     else:
-        orc.render(scene, cw, ch, 2, depth=depth, rng=oh.RNG_HASH)
+        orc.render(scene, cw, ch, 2, depth=depth, rng=oh.RNG_HASH, threads=cores)
     per_sample = (time.perf_counter() - t) / (cw * ch * 2)
     step_spp = max(1, min(spp, int(6.0 / (per_sample * w * h))))
     for _ in range(args.warmup if args.warmup < 2 else 1):
@@ -149,10 +150,11 @@ def cpu_baseline(w, h, spp, depth, scene_kind, budget_s=12.0):
     if ref is None:
         orc = oh.Oracle(fast=True)
         scene = orc.scene() if scene_kind == "reference" else (orc.scene(11, 0.0, 0.5) if scene_kind == "stress" else orc.scene(int(scene_kind[4:])))
-        run = lambda ww, hh, s: orc.render(scene, ww, hh, s, depth=depth, rng=oh.RNG_HASH)
+        run = lambda ww, hh, s: orc.render(scene, ww, hh, s, depth=depth, rng=oh.RNG_HASH, threads=cores)
     else:
-        run = lambda ww, hh, s: ref.render(ww, hh, s, depth)
+        run = lambda ww, hh, s: ref.render(ww, hh, s, depth, threads=cores)
     cw, ch = max(1, w // 8), max(1, h // 8)
+    run(cw, ch, 1)   # thread pool start-up stays out of the calibration
     t = time.perf_counter(); run(cw, ch, 2); per_sample = (time.perf_counter() - t) / (cw * ch * 2)
     s = max(1, min(spp, int(budget_s / (per_sample * w * h))))
     t = time.perf_counter(); _, st = run(w, h, s); dt = time.perf_counter() - t
@@ -248,6 +250,11 @@ def run_b200(args):
     clocks_rows = []
     dev_ms, wall, kernel_ms, rays, launches, cand = timed(step_resident, args.steps, clocks_rows)
     dev_ms_max = max_over_ranks(dev_ms)
+    per_rank_ms = [dev_ms]
+    if world > 1:
+        gathered = [torch.zeros(1, dtype=torch.float64, device=f"cuda:{local}") for _ in range(world)]
+        dist.all_gather(gathered, torch.tensor([dev_ms], dtype=torch.float64, device=f"cuda:{local}"))
+        per_rank_ms = [float(g.item()) for g in gathered]
     total_rays = sum_over_ranks(rays)
     kernel_ms_max = max_over_ranks(kernel_ms)
     for _ in range(1):
@@ -314,7 +321,8 @@ def run_b200(args):
                                      "achieved": (st.nodeVisits * 48 + st.sphereTests * 17) / (st.renderKernelMs * 1e-3) * 1e-12,
                                      "node_visits_per_ray": st.nodeVisits / max(1, st.rays), "sphere_tests_per_ray": st.sphereTests / max(1, st.rays)})
             line["roofline"]["frac"] = line["roofline"]["achieved"] / peak_tf
-        if not args.no_cpu and world >= 1:
+        line["per_rank_ms_per_step"] = [m / args.steps for m in per_rank_ms]
+        if not args.no_cpu and world == 1:   # rank 0 at N=1 only
             line["cpu_baseline"] = cpu_baseline(w, h, spp, depth, scene_kind)
         print(json.dumps(line), flush=True)
     barrier()

@@ -259,3 +259,11 @@ def test_lbvh_duplicates_and_coincident_centres(oracle, vcrt):
             assert_same(gpu, st, cpu, cst)
     finally:
         host.destroy()
+
+
+def test_first_generation_scan_kernel_agrees(oracle, gpu_scene):
+    # shape=1 selects the LDS-fed first-generation brute-force kernel (kept for A/B measurements)
+    cpu, cst = oracle.render(gpu_scene, 203, 113, 3)
+    for shape in (1, 0):
+        gpu, st = host.render(203, 113, 3, traversal=BRUTE, sample_chunks=1, shape=shape)
+        assert_same(gpu, st, cpu, cst)

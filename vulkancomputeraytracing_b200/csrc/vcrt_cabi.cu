@@ -10,6 +10,7 @@
 #include "vcrt_kernel_simple.cuh"
 #include "vcrt_kernel_scan.cuh"
 #include "vcrt_kernel_lbvh.cuh"
+#include "vcrt_kernel_scanu.cuh"
 
 #include <cub/device/device_radix_sort.cuh>
 
@@ -33,6 +34,7 @@ static cudaEvent_t cudaComputeEvents[4] = {nullptr, nullptr, nullptr, nullptr};
 static unsigned char* cudaComputeSceneBlob = nullptr;   // device copy of the SoA blob
 static SceneBlob cudaComputeSceneHeader;
 static bool cudaComputeSceneReady = false;
+static bool cudaComputeSceneInConstant = false;   // the filter table of the uniform-datapath scan is loaded
 struct SceneExtent { float centreMin[3], centreMax[3], radiusMin, radiusMax; };
 static SceneExtent cudaComputeSceneExtent;
 // LBVH over the scan spheres (device indices [0, scanCount)), built on first use after an upload
@@ -199,6 +201,26 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
         }
     }
     for (uint32_t j = scanCount; j < scanPad; j++) hot[j] = make_float4(0.f, 0.f, 0.f, -INFINITY);   // padding never passes
+    // second-generation scan (vcrt_kernel_scanu.cuh): (cx, cy, cz, |c|^2 - R2) in the constant bank, R2 = r^2 + kappa(|c|^2 + r^2)
+    cudaComputeSceneInConstant = scanPad <= (uint32_t)kMaxConstSpheres;
+    if (cudaComputeSceneInConstant && scanPad) {
+        float4* chot = (float4*)calloc(scanPad, sizeof(float4));
+        if (!chot) { free(host); delete[] order; return fail(VCRT_ERROR_OUT_OF_MEMORY, "scene table%s", ""); }
+        for (uint32_t j = 0; j < scanPad; j++) {
+            if (j >= scanCount) { chot[j] = make_float4(0.f, 0.f, 0.f, INFINITY); continue; }
+            const VcrtSphere& s = spheres[order[j]];
+            double cc = (double)s.center[0] * s.center[0] + (double)s.center[1] * s.center[1] + (double)s.center[2] * s.center[2];
+            double r2 = (double)s.radius * s.radius;
+            double bound = cc - (r2 + (double)kKappaU * (cc + r2)) * (1.0 + 1.0 / 4194304.0);
+            float f = (float)bound;
+            if ((double)f > bound) f = nextafterf(f, -INFINITY);   // rounded DOWN: can only let more spheres pass
+            chot[j] = make_float4(s.center[0], s.center[1], s.center[2], f);
+        }
+        cudaError_t ce = cudaMemcpyToSymbolAsync(cSceneHot, chot, (size_t)scanPad * sizeof(float4), 0, cudaMemcpyHostToDevice, cudaComputeStream);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(cudaComputeStream);
+        free(chot);
+        if (ce != cudaSuccess) { free(host); delete[] order; return fail(VCRT_ERROR_CUDA, "scene table upload: %s", cudaGetErrorString(ce)); }
+    }
     memcpy(host, &hdr, sizeof hdr);
     delete[] order;
 
@@ -544,6 +566,25 @@ static int launchScan(const RenderArgs& args, uint32_t* launches) {
     return VCRT_SUCCESS;
 }
 
+template <int THREADS, int PAIRS, int LCAP, bool FIXED>
+static int launchScanU(const RenderArgs& args, uint32_t* launches) {
+    using Cfg = ScanUConfig<THREADS, PAIRS, LCAP>;
+    const size_t smem = Cfg::smem_bytes(cudaComputeSceneHeader.bytes);
+    auto kernel = render_scanu_kernel<THREADS, PAIRS, LCAP, FIXED>;
+    CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned int grid = (unsigned int)cudaComputeSmCount;   // persistent: one CTA per SM
+    const unsigned int firstDynamicItem = grid * Cfg::R * THREADS;
+    CUDA_TRY(cudaMemcpyAsync(cudaComputeWorkCounter, &firstDynamicItem, sizeof firstDynamicItem, cudaMemcpyHostToDevice, cudaComputeStream));
+    kernel<<<grid, THREADS, smem, cudaComputeStream>>>(cudaComputeSceneBlob, args, (int)cudaComputeSceneHeader.scanPad);
+    CUDA_TRY(cudaGetLastError());
+    *launches += 1;
+    return VCRT_SUCCESS;
+}
+static bool scanUFits(int threads, int pairs, int lcap) {
+    size_t state = (size_t)SF_COUNT * 2 * pairs * threads * 4, lists = (size_t)lcap * threads * 2;
+    return cudaComputeSceneInConstant && 16 + (size_t)cudaComputeSceneHeader.bytes + state + lists <= 227 * 1024;
+}
+
 static const size_t kSmemBudget = 227 * 1024;
 static const uint32_t kBruteForceLimit = 1024;   // spheres; above this the LBVH is faster (measured)
 static bool scanFits(int threads, int pairs, int cap) {
@@ -617,7 +658,11 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     } else {
         // reserved[1]: experiment switch for the CTA shape (0 = default)
         const uint32_t shape = p->reserved[1];
-        if (shape == 2 && fixedMode && scanFits(1024, 1, 12)) rc = launchScan<1024, 1, 12, true>(args, &launches);
+        if ((shape == 0 || shape == 10) && scanUFits(512, 2, 30)) rc = fixedMode ? launchScanU<512, 2, 30, true>(args, &launches) : launchScanU<512, 2, 30, false>(args, &launches);
+        else if (shape == 11 && fixedMode && scanUFits(1024, 1, 30)) rc = launchScanU<1024, 1, 30, true>(args, &launches);
+        else if (shape == 12 && fixedMode && scanUFits(256, 4, 30)) rc = launchScanU<256, 4, 30, true>(args, &launches);
+        else if (shape == 13 && fixedMode && scanUFits(384, 3, 30)) rc = launchScanU<384, 3, 30, true>(args, &launches);
+        else if (shape == 2 && fixedMode && scanFits(1024, 1, 12)) rc = launchScan<1024, 1, 12, true>(args, &launches);
         else if (shape == 3 && fixedMode && scanFits(768, 1, 12)) rc = launchScan<768, 1, 12, true>(args, &launches);
         else if (shape == 4 && fixedMode && scanFits(640, 1, 12)) rc = launchScan<640, 1, 12, true>(args, &launches);
         else if (fixedMode) rc = wide ? launchScan<512, 2, 12, true>(args, &launches) : launchScan<256, 2, 12, true>(args, &launches);

@@ -303,7 +303,7 @@ def run_b200(args):
                     "d2h_bytes_per_step": int(host_image.nbytes), "timing": "wall clock around cudaUploadScene + cudaRender + cudaDownloadImage, max over ranks"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf if peak_tf else None,
-                         "traffic": None, "kernel": "render_scan_kernel" if host.stats().traversalUsed == 1 else "render_lbvh_kernel",
+                         "traffic": None, "kernel": "render_scanu_kernel" if host.stats().traversalUsed == 1 else "render_lbvh_kernel",
                          "kernel_ms_per_step": kernel_ms / args.steps, "kernel_share_of_step": kernel_ms / dev_ms if dev_ms else None,
                          "algorithmic": f"rays x {count} spheres x {FLOP_PER_TEST} flop (SURVEY.md 8d); rays from the in-kernel counter",
                          "peak_source": f"FFMA-only kernel measured live on this GPU (cudaMeasureFp32Peak, {peak_mhz:.0f} MHz effective); "

@@ -586,7 +586,7 @@ static bool scanUFits(int threads, int pairs, int lcap) {
 }
 
 static const size_t kSmemBudget = 227 * 1024;
-static const uint32_t kBruteForceLimit = 1024;   // spheres; above this the LBVH is faster (measured)
+static const uint32_t kBruteForceLimit = 48;   // spheres; above this VCRT_TRAVERSAL_AUTO takes the LBVH
 static bool scanFits(int threads, int pairs, int cap) {
     size_t state = (size_t)SF_COUNT * 2 * pairs * threads * 4, lists = (size_t)(cap + 2) * 2 * pairs * threads * 2;
     return 16 + (size_t)cudaComputeSceneHeader.bytes + state + lists <= kSmemBudget && cudaComputeSceneHeader.scanPad < 65536u;
@@ -600,10 +600,11 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     if (!cudaComputeSceneReady) return fail(VCRT_ERROR_NOT_READY, "cudaRender before cudaUploadScene%s", "");
 
     uint32_t traversal = p->traversal;
-    // AUTO: brute force (the reference's own algorithm) while the scene is small enough for it to win, else the LBVH
+    // AUTO = the fastest: the LBVH beats the brute-force scan from a few dozen spheres on (measured 2.0x at 485 spheres,
+    // DESIGN.md section 6); below that the tree has nothing to prune and the scan's regular inner loop wins
     if (traversal == VCRT_TRAVERSAL_AUTO)
-        traversal = (scanFits(256, 2, 12) && cudaComputeSceneHeader.count <= kBruteForceLimit) ? VCRT_TRAVERSAL_BRUTE : VCRT_TRAVERSAL_LBVH;
-    if (traversal == VCRT_TRAVERSAL_BRUTE && !scanFits(256, 2, 12))
+        traversal = (cudaComputeSceneHeader.count <= kBruteForceLimit && (scanUFits(1024, 1, 30) || scanFits(256, 2, 12))) ? VCRT_TRAVERSAL_BRUTE : VCRT_TRAVERSAL_LBVH;
+    if (traversal == VCRT_TRAVERSAL_BRUTE && !scanFits(256, 2, 12) && !scanUFits(512, 2, 30))
         return fail(VCRT_ERROR_UNSUPPORTED, "scene does not fit shared memory for VCRT_TRAVERSAL_BRUTE%s", "");
     if (traversal > VCRT_TRAVERSAL_SIMPLE) return fail(VCRT_ERROR_INVALID_ARGUMENT, "unknown traversal%s", "");
 
@@ -658,10 +659,11 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     } else {
         // reserved[1]: experiment switch for the CTA shape (0 = default)
         const uint32_t shape = p->reserved[1];
-        if ((shape == 0 || shape == 10) && scanUFits(512, 2, 30)) rc = fixedMode ? launchScanU<512, 2, 30, true>(args, &launches) : launchScanU<512, 2, 30, false>(args, &launches);
-        else if (shape == 11 && fixedMode && scanUFits(1024, 1, 30)) rc = launchScanU<1024, 1, 30, true>(args, &launches);
+        // default: 1024 threads x 2 rays (32 warps per SM hide the shading phases best; measured 94 ms vs 102 ms for 512 x 4
+        // at 1080p x 128 spp), falling back to 512 x 4 and then to the first-generation kernel as shared memory runs out
+        if ((shape == 0 || shape == 11) && scanUFits(1024, 1, 30)) rc = fixedMode ? launchScanU<1024, 1, 30, true>(args, &launches) : launchScanU<1024, 1, 30, false>(args, &launches);
+        else if ((shape == 0 || shape == 10) && scanUFits(512, 2, 30)) rc = fixedMode ? launchScanU<512, 2, 30, true>(args, &launches) : launchScanU<512, 2, 30, false>(args, &launches);
         else if (shape == 12 && fixedMode && scanUFits(256, 4, 30)) rc = launchScanU<256, 4, 30, true>(args, &launches);
-        else if (shape == 13 && fixedMode && scanUFits(384, 3, 30)) rc = launchScanU<384, 3, 30, true>(args, &launches);
         else if (shape == 2 && fixedMode && scanFits(1024, 1, 12)) rc = launchScan<1024, 1, 12, true>(args, &launches);
         else if (shape == 3 && fixedMode && scanFits(768, 1, 12)) rc = launchScan<768, 1, 12, true>(args, &launches);
         else if (shape == 4 && fixedMode && scanFits(640, 1, 12)) rc = launchScan<640, 1, 12, true>(args, &launches);

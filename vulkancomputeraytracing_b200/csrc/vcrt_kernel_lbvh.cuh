@@ -63,15 +63,14 @@ VCRT_DEV void hit_ordered(float4 shape, int device, uint32_t orig, const Ray& r,
 }
 
 template <bool FIXED>
-__global__ void __launch_bounds__(256, 2) render_lbvh_kernel(BvhScene scene, RenderArgs args) {
+__global__ void __launch_bounds__(256, 3) render_lbvh_kernel(BvhScene scene, RenderArgs args) {
     const uint32_t pixels = args.width * args.height;
     const uint32_t sppPerChunk = FIXED ? args.samplesPerItem : (args.spp + args.chunks - 1u) / args.chunks;
     const uint32_t runsPerPixel = (args.spp + sppPerChunk - 1u) / sppPerChunk;
     // items walk the image in 8x4 pixel tiles so a warp starts on one tile
     const uint32_t tilesX = (args.width + 7u) / 8u, tilesY = (args.height + 3u) / 4u, pixelsPadded = tilesX * tilesY * 32u;
     const uint32_t totalItems = pixelsPadded * runsPerPixel;
-    unsigned long long nRays = 0, nNodes = 0, nTests = 0;
-    uint32_t nExhausted = 0, nBad = 0;
+    uint32_t nRays = 0, nNodes = 0, nTests = 0, nExhausted = 0, nBad = 0;   // per thread; widened when summed
     int stack[64];
 
     uint32_t item = blockIdx.x * blockDim.x + threadIdx.x;
@@ -122,32 +121,43 @@ __global__ void __launch_bounds__(256, 2) render_lbvh_kernel(BvhScene scene, Ren
                         const float F2 = fmaf(fx, fx, fmaf(fy, fy, fz * fz));
                         const float K = 3.814697265625e-06f * (F2 + scene.radiusMax * scene.radiusMax);   // 64 eps, eps = 2^-24
                         const float grow = fminf(sqrtf(K), K / (2.f * scene.radiusMin)) * 1.0001f + 9.5367431640625e-07f * (sqrtf(oo) + sqrtf(F2));
-                        const float ix = 1.0f / ray.d.x, iy = 1.0f / ray.d.y, iz = 1.0f / ray.d.z;   // +-inf for zero components: slabs handle it
-                        const float bx = -ray.o.x * ix, by = -ray.o.y * iy, bz = -ray.o.z * iz;
-                        const float ex = grow * fabsf(ix), ey = grow * fabsf(iy), ez = grow * fabsf(iz);
+                        // slab constants per axis: t_near = near_plane * inv + bn, t_far = far_plane * inv + bf, where the near plane is
+                        // the box minimum when the direction component is >= 0 (picked with one select per plane) and bn / bf carry
+                        // the origin and the widening.  A component too small to invert safely leaves its axis unconstrained
+                        // (inv = 0, bn = -inf, bf = +inf): conservative.
+                        const bool px_ = ray.d.x >= 0.f, py_ = ray.d.y >= 0.f, pz_ = ray.d.z >= 0.f;
+                        const bool ux = fabsf(ray.d.x) > 1e-30f, uy = fabsf(ray.d.y) > 1e-30f, uz = fabsf(ray.d.z) > 1e-30f;
+                        const float ix = ux ? 1.0f / ray.d.x : 0.f, iy = uy ? 1.0f / ray.d.y : 0.f, iz = uz ? 1.0f / ray.d.z : 0.f;
+                        const float kInf = __int_as_float(0x7f800000);
+                        const float bnx = ux ? fmaf(-ray.o.x, ix, -grow * fabsf(ix)) : -kInf, bfx = ux ? fmaf(-ray.o.x, ix, grow * fabsf(ix)) : kInf;
+                        const float bny = uy ? fmaf(-ray.o.y, iy, -grow * fabsf(iy)) : -kInf, bfy = uy ? fmaf(-ray.o.y, iy, grow * fabsf(iy)) : kInf;
+                        const float bnz = uz ? fmaf(-ray.o.z, iz, -grow * fabsf(iz)) : -kInf, bfz = uz ? fmaf(-ray.o.z, iz, grow * fabsf(iz)) : kInf;
                         int sp = 0, node = 0;
                         for (;;) {
-                            nNodes++;
-                            const float4 na = __ldg(&scene.nodes[node].a), nb = __ldg(&scene.nodes[node].b), nc = __ldg(&scene.nodes[node].c);
-                            const int2 ch = __ldg(reinterpret_cast<const int2*>(&scene.nodes[node].child0));
-                            // fminf/fmaxf drop NaN (0 * inf when the origin lies on a slab plane of a zero component): the slab then does not constrain
-                            float t0, t1, n0, f0, n1, f1;
-                            t0 = fmaf(na.x, ix, bx); t1 = fmaf(na.w, ix, bx); n0 = fminf(t0, t1) - ex; f0 = fmaxf(t0, t1) + ex;
-                            t0 = fmaf(na.y, iy, by); t1 = fmaf(nb.x, iy, by); n0 = fmaxf(n0, fminf(t0, t1) - ey); f0 = fminf(f0, fmaxf(t0, t1) + ey);
-                            t0 = fmaf(na.z, iz, bz); t1 = fmaf(nb.y, iz, bz); n0 = fmaxf(n0, fminf(t0, t1) - ez); f0 = fminf(f0, fmaxf(t0, t1) + ez);
-                            t0 = fmaf(nb.z, ix, bx); t1 = fmaf(nc.y, ix, bx); n1 = fminf(t0, t1) - ex; f1 = fmaxf(t0, t1) + ex;
-                            t0 = fmaf(nb.w, iy, by); t1 = fmaf(nc.z, iy, by); n1 = fmaxf(n1, fminf(t0, t1) - ey); f1 = fminf(f1, fmaxf(t0, t1) + ey);
-                            t0 = fmaf(nc.x, iz, bz); t1 = fmaf(nc.w, iz, bz); n1 = fmaxf(n1, fminf(t0, t1) - ez); f1 = fminf(f1, fmaxf(t0, t1) + ez);
-                            // accepted roots lie in (t_min, rec.t]; a NaN interval bound (cannot arise from finite inputs) would pass
-                            bool h0 = !(n0 > f0) && !(f0 < 0.f) && !(n0 > rec.t);
-                            bool h1 = !(n1 > f1) && !(f1 < 0.f) && !(n1 > rec.t);
-                            int c0 = ch.x, c1 = ch.y;
-                            if (h0 && h1 && n1 < n0) { int t = c0; c0 = c1; c1 = t; }   // nearer child first
-                            else if (!h0) { c0 = c1; h0 = h1; h1 = false; }
-                            if (h0 && c0 < 0) { const int l = ~c0; hit_ordered(__ldg(&scene.leafShape[l]), (int)__ldg(&scene.leafDevice[l]), __ldg(&scene.leafOrig[l]), ray, a, rec); nTests++; h0 = false; }
-                            if (h1 && c1 < 0) { const int l = ~c1; hit_ordered(__ldg(&scene.leafShape[l]), (int)__ldg(&scene.leafDevice[l]), __ldg(&scene.leafOrig[l]), ray, a, rec); nTests++; h1 = false; }
-                            if (h0) { node = c0; if (h1) stack[sp++] = c1; continue; }
-                            if (h1) { node = c1; continue; }
+                            if (node >= 0) {
+                                nNodes++;
+                                const float4 na = __ldg(&scene.nodes[node].a), nb = __ldg(&scene.nodes[node].b), nc = __ldg(&scene.nodes[node].c);
+                                const int2 ch = __ldg(reinterpret_cast<const int2*>(&scene.nodes[node].child0));
+                                // child0: min (na.x, na.y, na.z) max (na.w, nb.x, nb.y); child1: min (nb.z, nb.w, nc.x) max (nc.y, nc.z, nc.w)
+                                const float n0 = fmaxf(fmaxf(fmaf(px_ ? na.x : na.w, ix, bnx), fmaf(py_ ? na.y : nb.x, iy, bny)), fmaf(pz_ ? na.z : nb.y, iz, bnz));
+                                const float f0 = fminf(fminf(fmaf(px_ ? na.w : na.x, ix, bfx), fmaf(py_ ? nb.x : na.y, iy, bfy)), fmaf(pz_ ? nb.y : na.z, iz, bfz));
+                                const float n1 = fmaxf(fmaxf(fmaf(px_ ? nb.z : nc.y, ix, bnx), fmaf(py_ ? nb.w : nc.z, iy, bny)), fmaf(pz_ ? nc.x : nc.w, iz, bnz));
+                                const float f1 = fminf(fminf(fmaf(px_ ? nc.y : nb.z, ix, bfx), fmaf(py_ ? nc.z : nb.w, iy, bfy)), fmaf(pz_ ? nc.w : nc.x, iz, bfz));
+                                // accepted roots lie in (t_min, rec.t]
+                                const bool h0 = !(n0 > f0) && !(f0 < 0.f) && !(n0 > rec.t);   // written so that a NaN bound passes
+                                const bool h1 = !(n1 > f1) && !(f1 < 0.f) && !(n1 > rec.t);
+                                if (h0 && h1) {   // nearer child first, the other one waits on the stack
+                                    const bool swap = n1 < n0;
+                                    node = swap ? ch.y : ch.x;
+                                    stack[sp++] = swap ? ch.x : ch.y;
+                                    continue;
+                                }
+                                if (h0 || h1) { node = h0 ? ch.x : ch.y; continue; }
+                            } else {      // a leaf: the exact test
+                                const int l = ~node;
+                                hit_ordered(__ldg(&scene.leafShape[l]), (int)__ldg(&scene.leafDevice[l]), __ldg(&scene.leafOrig[l]), ray, a, rec);
+                                nTests++;
+                            }
                             if (sp == 0) break;
                             node = stack[--sp];
                         }
@@ -171,13 +181,14 @@ __global__ void __launch_bounds__(256, 2) render_lbvh_kernel(BvhScene scene, Ren
         if (!FIXED) args.sums[(size_t)chunk * pixels + pixel] = make_float4(sum.x, sum.y, sum.z, 0.f);
     }
     // one atomic per warp per counter
+    unsigned long long wRays = nRays, wNodes = nNodes, wTests = nTests;
     for (int off = 16; off > 0; off >>= 1) {
-        nRays += __shfl_down_sync(0xffffffffu, nRays, off); nNodes += __shfl_down_sync(0xffffffffu, nNodes, off);
-        nTests += __shfl_down_sync(0xffffffffu, nTests, off);
+        wRays += __shfl_down_sync(0xffffffffu, wRays, off); wNodes += __shfl_down_sync(0xffffffffu, wNodes, off);
+        wTests += __shfl_down_sync(0xffffffffu, wTests, off);
         nExhausted += __shfl_down_sync(0xffffffffu, nExhausted, off); nBad += __shfl_down_sync(0xffffffffu, nBad, off);
     }
     if ((threadIdx.x & 31) == 0) {
-        atomicAdd(&args.counters[CTR_RAYS], nRays); atomicAdd(&args.counters[CTR_NODES], nNodes); atomicAdd(&args.counters[CTR_TESTS], nTests);
+        atomicAdd(&args.counters[CTR_RAYS], wRays); atomicAdd(&args.counters[CTR_NODES], wNodes); atomicAdd(&args.counters[CTR_TESTS], wTests);
         if (nExhausted) atomicAdd(&args.counters[CTR_EXHAUSTED], (unsigned long long)nExhausted);
         if (nBad) atomicAdd(&args.counters[CTR_BAD_MATERIAL], (unsigned long long)nBad);
     }

@@ -38,8 +38,9 @@ VCRT_DEV Ray primary_ray(const Frame& f, uint32_t px, uint32_t py, float ju, flo
 
 // functions.glsl:85-89: sky colour seen along d.  mix(vec3(1), vec3(.5,.7,1), a)
 VCRT_DEV V3 sky(V3 d) {
-    V3 unit_direction = vunit(d);
-    float a = fmul(0.5f, fadd(unit_direction.y, 1.0f));
+    // normalize(d).y is the only component used: d.y / length(d), the same two operations the full normalize applies to y
+    float unit_y = fdiv(d.y, fsqrt(vdot(d, d)));
+    float a = fmul(0.5f, fadd(unit_y, 1.0f));
     float ia = fsub(1.0f, a);
     return v3(fadd(fmul(1.f, ia), fmul(.5f, a)), fadd(fmul(1.f, ia), fmul(.7f, a)), fadd(fmul(1.f, ia), fmul(1.f, a)));
 }
@@ -79,16 +80,16 @@ VCRT_DEV bool scatter(const float4 shape, const float4 surf, int kind, float t, 
     V3 normal = vdiv(vsub(point, v3(shape.x, shape.y, shape.z)), shape.w);      // functions.glsl:36, outward
     V3 albedo = v3(surf.x, surf.y, surf.z);
     float param = surf.w;
-    if (kind == 1) {  // lambertian, textures.glsl:19-25 (bug B4b: extra * texture.y)
-        V3 direction = vadd(normal, random_in_unit_sphere(u));
-        colour = vscale(vmul(colour, albedo), param);
-        ray.o = point; ray.d = direction;
-        return true;
-    }
-    if (kind == 2) {  // metal, textures.glsl:58-63
-        V3 direction = vadd(vreflect(ray.d, normal), vscale(random_in_unit_sphere(u), param));
-        colour = vmul(colour, albedo);
-        ray.o = point; ray.d = direction;
+    if (kind == 1 || kind == 2) {
+        // lambertian (textures.glsl:19-25; bug B4b: extra * texture.y) and metal (textures.glsl:58-63) share their one expensive
+        // step, the unit vector of functions.glsl:42-44, so a warp with both materials walks it once instead of twice
+        const V3 rv = random_in_unit_sphere(u);
+        const bool lambert = kind == 1;
+        const V3 base = lambert ? normal : vreflect(ray.d, normal);
+        const V3 offset = lambert ? rv : vscale(rv, param);
+        const V3 tint = vmul(colour, albedo);
+        colour = lambert ? vscale(tint, param) : tint;
+        ray.o = point; ray.d = vadd(base, offset);
         return true;
     }
     if (kind == 3) {  // glass, textures.glsl:27-56

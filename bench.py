@@ -216,11 +216,11 @@ def run_b200(args):
     def timed(step, steps, clocks_rows=None):
         """K steps, each bracketed by CUDA events on the layer's stream; L2 flushed between steps. Returns per-rank
         device ms (sum), wall s, and the per-step stats."""
-        barrier()
         stop = threading.Event(); sampler = None
         if clocks_rows is not None and rank == 0:
             sampler = threading.Thread(target=clock_sampler, args=(stop, clocks_rows, local), daemon=True); sampler.start()
             time.sleep(0.3)
+        barrier()   # after the sampler start-up: a late rank would otherwise make the others wait inside their first reduce
         dev_ms, kernel_ms, rays, launches, cand = 0.0, 0.0, 0, 0, 0
         t0 = time.perf_counter()
         for _ in range(steps):

@@ -40,6 +40,7 @@ typedef struct RendererConfiguration {
     uint32_t frames;               /* event-loop iterations of the headless platform */
     uint32_t progressive;          /* 0: every frame re-renders from scratch (what the reference does); 1: frames accumulate */
     uint32_t traversal;            /* VCRT_TRAVERSAL_* */
+    uint32_t semantics;            /* VCRT_SEMANTICS_*: the reference shader as it is, or the BOOK-corrected path */
     uint32_t sceneGridHalf;        /* 11 = the reference scene */
     uint32_t sceneVariant;         /* VCRT_SCENE_* */
     uint64_t seed;

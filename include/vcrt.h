@@ -74,6 +74,14 @@ enum {
     VCRT_FLAG_COUNT_STATS = 1u << 3   /* also fill the per-material / path-length counters (slower) */
 };
 
+/* What the path computes.  REFERENCE = the reference shader as it is, bugs B1/B3/B4/B4b/B5/B8 included: the
+   parity mode and the default.  BOOK = the same path with those bugs fixed the way "Ray Tracing in One Weekend" writes the
+   routines (centred viewport, unit-sphere scatter, face-forwarded normals, real Snell/Schlick, gamma 2 on the result). */
+enum {
+    VCRT_SEMANTICS_REFERENCE = 0,
+    VCRT_SEMANTICS_BOOK = 1
+};
+
 /* Run-time stand-ins for the shader's compile-time constants (globals.glsl:9-17).
    Zero-initialise, then set what you need; vcrtDefaultRenderParams() gives the reference's
    values (1280x720, 1 spp, depth 50). */
@@ -88,7 +96,8 @@ typedef struct VcrtRenderParams {
     uint32_t traversal;        /* VCRT_TRAVERSAL_* */
     uint32_t flags;            /* VCRT_FLAG_* */
     uint32_t sampleChunks;     /* 0 = auto; 1 = a pixel's samples are summed strictly in index order */
-    uint32_t reserved[3];
+    uint32_t reserved[2];      /* must be 0 (development switches) */
+    uint32_t semantics;        /* VCRT_SEMANTICS_* */
 } VcrtRenderParams;
 
 /* Counters of the last cudaRender on this device. */

@@ -406,3 +406,175 @@ int oracle_generate_scene(int grid_half, double lambert_below, double metal_belo
     return n;
 }
 }
+
+// ====================================================================== BOOK semantics
+// TEST INFRASTRUCTURE.  Checker for the product's VCRT_SEMANTICS_BOOK mode: the same
+// path with the reference's MATCHED bugs fixed the way "Ray Tracing in One Weekend" (P. Shirley,
+// T. D. Black, S. Hollasch; v4.0.1, 2024 -- a third-party text that is NOT part of /root/reference)
+// writes them.  PARITY UNPINNED for this mode: the reference repository contains no book-mode code
+// or vectors, so this section restates the book's published listings (camera::initialize/get_ray,
+// sphere::hit + set_face_normal, lambertian/metal/dielectric::scatter, reflect/refract/reflectance,
+// random_unit_vector, ray_color, linear_to_gamma) in binary32, and is checked only by its own
+// invariants in tests/ (energy bounds, symmetry, convergence) and against the CUDA kernels.
+//   B1  -> viewport_width = viewport_height * (W / H as reals); pixel deltas divide by W and by H
+//   B3/B5/B6 -> directions are normalised where the book normalises them (metal reflect, dielectric)
+//   B4  -> random_unit_vector(): rejection sampling in the cube, uniform on the sphere
+//   B4b -> lambertian attenuation = albedo (texture.y ignored)
+//   normals are face-forwarded; metal absorbs below-surface scatter; Schlick with the real cosine
+//   B8  -> gamma 2 on the final mean (linear_to_gamma)
+// Draws: Philox block (pixel, sample, k, j): k = 0 pixel jitter; k >= 1 the k-th scatter event, j = attempt
+// index of its rejection loop (uniforms 0..2), the dielectric's reflectance draw = uniform 3 of attempt 0.
+namespace {
+
+inline Frame make_frame_book(const float* cam, int width, int height) {
+    V3 lookfrom = v3(cam[0], cam[1], cam[2]), lookat = v3(cam[3], cam[4], cam[5]), vup = v3(cam[6], cam[7], cam[8]);
+    float focal_length = len3(sub(lookfrom, lookat));
+    float theta = cam[9] * 0.017453292519943295f;
+    float h = std::tan(theta / 2);
+    float viewport_height = 2 * h * focal_length;
+    float viewport_width = viewport_height * ((float)width / (float)height);
+    V3 w = unit(sub(lookfrom, lookat));
+    V3 u = unit(cross3(vup, w));
+    V3 v = cross3(w, u);
+    V3 viewport_u = lscale(viewport_width, u);
+    V3 viewport_v = lscale(viewport_height, neg(v));
+    Frame f;
+    f.du = divs(viewport_u, (float)width);
+    f.dv = divs(viewport_v, (float)height);
+    V3 upper_left = sub(sub(sub(lookfrom, lscale(focal_length, w)), divs(viewport_u, 2.f)), divs(viewport_v, 2.f));
+    f.pixel00 = add(upper_left, lscale(0.5f, add(f.du, f.dv)));
+    f.center = lookfrom;
+    return f;
+}
+
+struct BookRng { uint32_t key[2], pixel, sample, event; };
+inline void book_block(const BookRng& g, uint32_t attempt, float u[4]) {
+    uint32_t ctr[4] = {g.pixel, g.sample, g.event, attempt}, r[4];
+    philox4x32_10(ctr, g.key, r);
+    for (int i = 0; i < 4; i++) u[i] = u01(r[i]);
+}
+// random_unit_vector(): p uniform in [-1,1)^3 until 1e-30 < |p|^2 <= 1; p / |p|.  `first` = attempt-0 block (already drawn).
+inline V3 book_unit_vector(const BookRng& g, const float first[4]) {
+    float u[4] = {first[0], first[1], first[2], first[3]};
+    for (uint32_t attempt = 0;; attempt++) {
+        V3 p = v3(2.f * u[0] - 1.f, 2.f * u[1] - 1.f, 2.f * u[2] - 1.f);
+        float lensq = dot3(p, p);
+        if (1e-30f < lensq && lensq <= 1.f) return divs(p, std::sqrt(lensq));
+        if (attempt == 63u) return v3(1.f, 0.f, 0.f);   // probability (1 - pi/6)^64 ~ 1e-21
+        book_block(g, attempt + 1u, u);
+    }
+}
+inline float book_reflectance(float cosine, float ri) {
+    float r0 = (1.f - ri) / (1.f + ri);
+    r0 = r0 * r0;
+    float x = 1.f - cosine, x2 = x * x;
+    return r0 + (1.f - r0) * (x2 * x2 * x);   // pow(1 - cosine, 5) as multiplies: identical on CPU and GPU
+}
+
+inline V3 ray_color_book(Ray r, const Sphere* world, int count, int max_depth, BookRng g, Stats& st) {
+    V3 color = v3(1.f, 1.f, 1.f);
+    Hit rec;
+    for (int pass = 0; pass < max_depth; pass++) {
+        st.rays++;
+        bool any = false;
+        rec.max_t = 1e5f; rec.min_t = 0.001f;
+        for (int i = 0; i < count; i++)
+            if (hit_sphere(world[i], r, rec)) any = true;
+        if (!any) {
+            V3 unit_direction = unit(r.direction);
+            float a = 0.5f * (unit_direction.y + 1.0f);
+            st.path_hist[pass < 7 ? pass : 7]++;
+            return mul(color, add(scale(v3(1.f, 1.f, 1.f), 1.0f - a), scale(v3(.5f, .7f, 1.f), a)));
+        }
+        g.event = (uint32_t)pass + 1u;
+        float u[4]; book_block(g, 0u, u);
+        int kind = (int)rec.texture.x;
+        if (kind >= 1 && kind <= 3) st.hits[kind]++; else st.hits[0]++;
+        bool front_face = dot3(r.direction, rec.normal) < 0.f;           // set_face_normal
+        V3 normal = front_face ? rec.normal : neg(rec.normal);
+        if (kind == 1) {
+            V3 direction = add(normal, book_unit_vector(g, u));
+            const float s = 1e-8f;
+            if (std::fabs(direction.x) < s && std::fabs(direction.y) < s && std::fabs(direction.z) < s) direction = normal;
+            color = mul(color, rec.colour);
+            r.origin = rec.point; r.direction = direction;
+        } else if (kind == 2) {
+            float fuzz = rec.texture.y < 1.f ? rec.texture.y : 1.f;
+            V3 reflected = sub(r.direction, lscale(2.f * dot3(r.direction, normal), normal));
+            reflected = add(unit(reflected), lscale(fuzz, book_unit_vector(g, u)));
+            color = mul(color, rec.colour);
+            r.origin = rec.point; r.direction = reflected;
+            if (!(dot3(reflected, normal) > 0.f)) return v3(0.f, 0.f, 0.f);   // absorbed
+        } else if (kind == 3) {
+            float ri = front_face ? (1.0f / rec.texture.y) : rec.texture.y;
+            V3 ud = unit(r.direction);
+            float cos_theta = std::fmin(dot3(neg(ud), normal), 1.0f);
+            float sin_theta = std::sqrt(1.0f - cos_theta * cos_theta);
+            V3 direction;
+            if (ri * sin_theta > 1.0f || book_reflectance(cos_theta, ri) > u[3])
+                direction = sub(ud, lscale(2.f * dot3(ud, normal), normal));
+            else {
+                V3 perp = lscale(ri, add(ud, lscale(cos_theta, normal)));
+                V3 parallel = lscale(-std::sqrt(std::fabs(1.0f - dot3(perp, perp))), normal);
+                direction = add(perp, parallel);
+            }
+            r.origin = rec.point; r.direction = direction;
+        } else return v3(0.f, 0.f, 0.f);   // unknown material: no scatter
+    }
+    st.exhausted++;
+    return v3(0.f, 0.f, 0.f);
+}
+
+}  // namespace
+
+extern "C" int oracle_render_book(const float* spheres, int count, const float* camera, int width, int height, int spp,
+                                  int sample_offset, int max_depth, uint64_t seed, int normalise, int threads,
+                                  float* rgba, uint64_t* stats) {
+    if (!spheres || !camera || !rgba || count < 0 || width <= 0 || height <= 0 || spp <= 0 || max_depth < 0) return -1;
+    const Sphere* world = reinterpret_cast<const Sphere*>(spheres);
+    Frame f = make_frame_book(camera, width, height);
+    Stats total; std::memset(&total, 0, sizeof(total));
+    if (threads > 0) omp_set_num_threads(threads);
+#pragma omp parallel
+    {
+        Stats st; std::memset(&st, 0, sizeof(st));
+#pragma omp for schedule(dynamic, 1) nowait
+        for (int y = 0; y < height; y++) {
+            for (int x = 0; x < width; x++) {
+                V3 pixel_center = add(add(f.pixel00, lscale((float)x, f.du)), lscale((float)y, f.dv));
+                V3 sum = v3(0.f, 0.f, 0.f);
+                BookRng g; g.key[0] = (uint32_t)seed; g.key[1] = (uint32_t)(seed >> 32); g.pixel = (uint32_t)(y * width + x);
+                for (int s = 0; s < spp; s++) {
+                    g.sample = (uint32_t)(sample_offset + s); g.event = 0u;
+                    float u[4]; book_block(g, 0u, u);
+                    V3 pixel_sample = add(pixel_center, add(lscale(-0.5f + u[0], f.du), lscale(-0.5f + u[1], f.dv)));
+                    Ray r; r.origin = f.center; r.direction = sub(pixel_sample, f.center);
+                    sum = add(sum, ray_color_book(r, world, count, max_depth, g, st));
+                }
+                if (normalise) {   // mean, then linear_to_gamma
+                    sum = divs(sum, (float)spp);
+                    sum = v3(sum.x > 0.f ? std::sqrt(sum.x) : 0.f, sum.y > 0.f ? std::sqrt(sum.y) : 0.f, sum.z > 0.f ? std::sqrt(sum.z) : 0.f);
+                }
+                float* px = rgba + 4 * ((size_t)y * width + x);
+                px[0] = sum.x; px[1] = sum.y; px[2] = sum.z; px[3] = 1.0f;
+            }
+        }
+#pragma omp critical
+        {
+            total.rays += st.rays; total.exhausted += st.exhausted;
+            for (int i = 0; i < 4; i++) total.hits[i] += st.hits[i];
+            for (int i = 0; i < 8; i++) total.path_hist[i] += st.path_hist[i];
+        }
+    }
+    if (stats) {
+        stats[0] = total.rays; stats[1] = total.exhausted;
+        for (int i = 0; i < 4; i++) stats[2 + i] = total.hits[i];
+        for (int i = 0; i < 8; i++) stats[6 + i] = total.path_hist[i];
+    }
+    return 0;
+}
+extern "C" void oracle_camera_book(const float* camera, int width, int height, float* out) {
+    Frame f = make_frame_book(camera, width, height);
+    const V3 v[4] = {f.center, f.pixel00, f.du, f.dv};
+    for (int i = 0; i < 4; i++) { out[3 * i] = v[i].x; out[3 * i + 1] = v[i].y; out[3 * i + 2] = v[i].z; }
+}

@@ -37,6 +37,8 @@ class Oracle:
         L.oracle_philox.argtypes = [VP, VP, VP]
         L.oracle_camera.argtypes = [VP, ctypes.c_int, ctypes.c_int, VP]
         L.oracle_first_hit.argtypes = [VP, ctypes.c_int, VP, VP, VP]
+        L.oracle_render_book.argtypes = [VP, ctypes.c_int, VP] + [ctypes.c_int] * 5 + [ctypes.c_uint64, ctypes.c_int, ctypes.c_int, VP, VP]
+        L.oracle_camera_book.argtypes = [VP, ctypes.c_int, ctypes.c_int, VP]
 
     def scene(self, grid_half=11, lambert_below=0.8, metal_below=0.95):
         cap = 4 * grid_half * grid_half + 4
@@ -59,10 +61,22 @@ class Oracle:
                  "path_hist": [int(x) for x in st[6:14]]}
         return img, stats
 
-    def camera(self, width, height, camera=CAMERA):
+    def render_book(self, spheres, width, height, spp, depth=50, seed=0, sample_offset=0, normalise=True, threads=0, camera=CAMERA):
+        """BOOK semantics: the book's routines in binary32; parity unpinned (see the oracle source)."""
+        spheres = np.ascontiguousarray(spheres, np.float32)
+        img = np.zeros((height, width, 4), np.float32)
+        st = np.zeros(14, np.uint64)
+        cam = np.ascontiguousarray(camera, np.float32)
+        rc = self.lib.oracle_render_book(spheres.ctypes.data_as(VP), spheres.shape[0], cam.ctypes.data_as(VP), width, height, spp,
+                                         sample_offset, depth, seed, 1 if normalise else 0, threads, img.ctypes.data_as(VP),
+                                         st.ctypes.data_as(VP))
+        assert rc == 0
+        return img, {"rays": int(st[0]), "exhausted": int(st[1]), "hits": [int(x) for x in st[2:6]], "path_hist": [int(x) for x in st[6:14]]}
+
+    def camera(self, width, height, camera=CAMERA, book=False):
         out = np.zeros(12, np.float32)
         cam = np.ascontiguousarray(camera, np.float32)
-        self.lib.oracle_camera(cam.ctypes.data_as(VP), width, height, out.ctypes.data_as(VP))
+        (self.lib.oracle_camera_book if book else self.lib.oracle_camera)(cam.ctypes.data_as(VP), width, height, out.ctypes.data_as(VP))
         return {"center": out[0:3], "pixel00": out[3:6], "du": out[6:9], "dv": out[9:12]}
 
     def first_hit(self, spheres, origin, direction):

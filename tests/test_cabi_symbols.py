@@ -36,7 +36,7 @@ def test_every_declared_symbol_is_exported_and_bound(vcrt):
 def test_struct_layouts():
     assert ctypes.sizeof(cabi.VcrtSphere) == 40          # structures.glsl:10-16, 10 floats
     assert ctypes.sizeof(cabi.VcrtCamera) == 40
-    assert ctypes.sizeof(cabi.VcrtRenderParams) == 56
+    assert ctypes.sizeof(cabi.VcrtRenderParams) == 56 and cabi.VcrtRenderParams.semantics.offset == 52
     assert cabi.VcrtRenderParams.seed.offset == 16 and cabi.VcrtRenderParams.sampleOffset.offset == 24
     assert ctypes.sizeof(cabi.VcrtRenderStats) == 8 * 8 + 4 * 8 + 8 * 8 + 6 * 4
     assert ctypes.sizeof(cabi.VcrtSceneRecipe) == 24

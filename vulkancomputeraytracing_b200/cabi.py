@@ -40,7 +40,7 @@ class VcrtRenderParams(ctypes.Structure):
     _fields_ = [("width", ctypes.c_uint32), ("height", ctypes.c_uint32), ("samplesPerPixel", ctypes.c_uint32),
                 ("maxDepth", ctypes.c_uint32), ("seed", ctypes.c_uint64), ("sampleOffset", ctypes.c_uint32),
                 ("totalSamples", ctypes.c_uint32), ("traversal", ctypes.c_uint32), ("flags", ctypes.c_uint32),
-                ("sampleChunks", ctypes.c_uint32), ("reserved", ctypes.c_uint32 * 3)]
+                ("sampleChunks", ctypes.c_uint32), ("reserved", ctypes.c_uint32 * 2), ("semantics", ctypes.c_uint32)]
 
 
 class VcrtRenderStats(ctypes.Structure):
@@ -58,6 +58,7 @@ class VcrtSceneRecipe(ctypes.Structure):
 
 
 VCRT_SCENE_REFERENCE, VCRT_SCENE_STRESS = 0, 1
+VCRT_SEMANTICS_REFERENCE, VCRT_SEMANTICS_BOOK = 0, 1
 
 
 class VcrtError(RuntimeError):

@@ -243,7 +243,7 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
 
 // shader.comp:18-39 in binary32, one rounding per operation (x86-64 host code has no FMA
 // contraction without -march flags; the build also passes -ffp-contract=off).
-static Frame makeFrame(const VcrtCamera& cam, uint32_t width, uint32_t height) {
+static Frame makeFrame(const VcrtCamera& cam, uint32_t width, uint32_t height, bool book) {
     struct H3 { float x, y, z; };
     auto sub = [](H3 a, H3 b) { return H3{a.x - b.x, a.y - b.y, a.z - b.z}; };
     auto lscale = [](float s, H3 a) { return H3{s * a.x, s * a.y, s * a.z}; };
@@ -258,13 +258,13 @@ static Frame makeFrame(const VcrtCamera& cam, uint32_t width, uint32_t height) {
     float theta = cam.vfov * 0.017453292519943295f;
     float h = tanf(theta / 2);
     float viewport_height = 2 * h * focal_length;
-    float viewport_width = viewport_height * (float)(width / height);   // bug B1: integer division
+    float viewport_width = viewport_height * (book ? (float)width / (float)height : (float)(width / height));   // bug B1: integer division
     H3 w = unit(sub(lookfrom, lookat));
     H3 u = unit(cross(vup, w));
     H3 v = cross(w, u);
     H3 viewport_u = lscale(viewport_width, u);
     H3 viewport_v = lscale(viewport_height, H3{-v.x, -v.y, -v.z});
-    H3 du = divs(viewport_u, (float)height);                            // bug B1: both deltas / HEIGHT
+    H3 du = divs(viewport_u, book ? (float)width : (float)height);      // bug B1: both deltas / HEIGHT
     H3 dv = divs(viewport_v, (float)height);
     H3 upper_left = sub(sub(sub(lookfrom, lscale(focal_length, w)), divs(viewport_u, 2.f)), divs(viewport_v, 2.f));
     H3 p00 = add(upper_left, lscale(0.5f, add(du, dv)));
@@ -287,11 +287,13 @@ __global__ void combine_planes_kernel(float4* accumulated, const float4* planes,
     accumulated[p] = a;
 }
 // shader.comp:56-57: color.rgb /= SAMPLES_PER_PIXEL; alpha stays 1 (shader.comp:44).
-__global__ void normalise_kernel(float4* image, const float4* sums, uint32_t pixels, float samples) {
+// gamma != 0 (BOOK semantics): linear_to_gamma of the book, sqrt of the mean.
+__device__ __forceinline__ float to_gamma(float v, int gamma) { return gamma ? (v > 0.f ? __fsqrt_rn(v) : 0.f) : v; }
+__global__ void normalise_kernel(float4* image, const float4* sums, uint32_t pixels, float samples, int gamma) {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= pixels) return;
     float4 s = sums[p];
-    image[p] = make_float4(__fdiv_rn(s.x, samples), __fdiv_rn(s.y, samples), __fdiv_rn(s.z, samples), 1.0f);
+    image[p] = make_float4(to_gamma(__fdiv_rn(s.x, samples), gamma), to_gamma(__fdiv_rn(s.y, samples), gamma), to_gamma(__fdiv_rn(s.z, samples), gamma), 1.0f);
 }
 // Fixed-point sums -> float sums (for cudaDownloadSums) and -> the normalised image.
 __global__ void fixed_to_float_kernel(float4* sums, const long long* fixedSums, uint32_t pixels) {
@@ -301,12 +303,12 @@ __global__ void fixed_to_float_kernel(float4* sums, const long long* fixedSums, 
     const double s = 1.0 / 4294967296.0;
     sums[p] = make_float4((float)((double)f[0] * s), (float)((double)f[1] * s), (float)((double)f[2] * s), 0.f);
 }
-__global__ void normalise_fixed_kernel(float4* image, const long long* fixedSums, uint32_t pixels, double samples) {
+__global__ void normalise_fixed_kernel(float4* image, const long long* fixedSums, uint32_t pixels, double samples, int gamma) {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= pixels) return;
     const long long* f = fixedSums + 4 * (size_t)p;
     const double s = 1.0 / (4294967296.0 * samples);
-    image[p] = make_float4((float)((double)f[0] * s), (float)((double)f[1] * s), (float)((double)f[2] * s), 1.0f);
+    image[p] = make_float4(to_gamma((float)((double)f[0] * s), gamma), to_gamma((float)((double)f[1] * s), gamma), to_gamma((float)((double)f[2] * s), gamma), 1.0f);
 }
 // FFMA-only kernel: the measured FP32 roofline denominator.
 __global__ void fp32_peak_kernel(float* out, int iters, float a, float b, long long* cycles) {
@@ -629,7 +631,10 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         return fail(VCRT_ERROR_UNSUPPORTED, "VCRT_FLAG_ACCUMULATE across different accumulation modes%s", "");
 
     RenderArgs args; memset(&args, 0, sizeof args);
-    args.frame = makeFrame(cudaComputeCamera, p->width, p->height);
+    if (p->semantics > VCRT_SEMANTICS_BOOK) return fail(VCRT_ERROR_INVALID_ARGUMENT, "unknown semantics%s", "");
+    const bool book = p->semantics == VCRT_SEMANTICS_BOOK;
+    args.frame = makeFrame(cudaComputeCamera, p->width, p->height, book);
+    args.semantics = p->semantics;
     args.width = p->width; args.height = p->height; args.spp = p->samplesPerPixel; args.sampleOffset = p->sampleOffset;
     args.maxDepth = p->maxDepth; args.seedLo = (uint32_t)p->seed; args.seedHi = (uint32_t)(p->seed >> 32);
     args.chunks = chunks; args.flags = p->flags; args.sums = cudaComputeSumPlanes;
@@ -699,8 +704,8 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     }
     if (p->totalSamples) totalSamples = p->totalSamples;
     if (haveImage) {
-        if (fixedSums) normalise_fixed_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeResultImage, finalFixed, pixels, (double)totalSamples);
-        else normalise_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeResultImage, finalSums, pixels, (float)totalSamples);
+        if (fixedSums) normalise_fixed_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeResultImage, finalFixed, pixels, (double)totalSamples, book ? 1 : 0);
+        else normalise_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeResultImage, finalSums, pixels, (float)totalSamples, book ? 1 : 0);
         launches++;
     }
     CUDA_TRY(cudaGetLastError());

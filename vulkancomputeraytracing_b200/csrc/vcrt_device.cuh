@@ -97,6 +97,7 @@ struct RenderArgs {
     float4* sums;           // float modes: [chunks][height*width] (x,y,z = sums, w unused)
     long long* fixedSums;   // fixed-point mode: [height*width][4] signed 32.32 sums (r, g, b, unused)
     uint32_t samplesPerItem;  // fixed-point mode: samples per work item
+    uint32_t semantics;       // 0 = the reference shader as it is, 1 = BOOK (vcrt_shade.cuh)
     unsigned long long* counters;  // see Counter enum
     unsigned int* workCounter;     // dynamic item dispenser
 };

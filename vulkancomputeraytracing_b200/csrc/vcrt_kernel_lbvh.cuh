@@ -166,9 +166,12 @@ __global__ void __launch_bounds__(256, 3) render_lbvh_kernel(BvhScene scene, Ren
                 if (rec.device < 0) { result = vmul(colour, sky(ray.d)); finished = true; break; }
                 philox4x32_10(pixel, sample, pass + 1u, 0u, args.seedLo, args.seedHi, rnd);
                 float u[4] = {u01(rnd[0]), u01(rnd[1]), u01(rnd[2]), u01(rnd[3])};
-                if (!scatter(__ldg(&scene.shape[rec.device]), __ldg(&scene.surf[rec.device]), __ldg(&scene.kind[rec.device]), rec.t, ray, colour, u)) {
-                    nBad++; finished = true; break;
-                }
+                int outcome;   // 0 = unknown material, 1 = scattered, 2 = absorbed by the material (BOOK metal)
+                if (args.semantics) {
+                    BookDraws g; g.pixel = pixel; g.sample = sample; g.event = pass + 1u; g.seedLo = args.seedLo; g.seedHi = args.seedHi;
+                    outcome = scatter_book(__ldg(&scene.shape[rec.device]), __ldg(&scene.surf[rec.device]), __ldg(&scene.kind[rec.device]), rec.t, ray, colour, u, g);
+                } else outcome = scatter(__ldg(&scene.shape[rec.device]), __ldg(&scene.surf[rec.device]), __ldg(&scene.kind[rec.device]), rec.t, ray, colour, u) ? 1 : 0;
+                if (outcome != 1) { if (outcome == 0) nBad++; finished = true; break; }
             }
             if (!finished) nExhausted++;
             if (FIXED) {

@@ -222,7 +222,13 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                     uint32_t rnd[4];
                     philox4x32_10(pixel, args.sampleOffset + ST(SF_SAMPLE, r), pass + 1u, 0u, args.seedLo, args.seedHi, rnd);
                     float u[4] = {u01(rnd[0]), u01(rnd[1]), u01(rnd[2]), u01(rnd[3])};
-                    if (!scatter(sShape[rec.index], sSurf[rec.index], sKind[rec.index], rec.t, ray, colour, u)) nBad++;
+                    int outcome;   // 0 = unknown material, 1 = scattered, 2 = absorbed by the material (BOOK metal)
+                    if (args.semantics) {
+                        BookDraws g; g.pixel = pixel; g.sample = args.sampleOffset + ST(SF_SAMPLE, r); g.event = pass + 1u; g.seedLo = args.seedLo; g.seedHi = args.seedHi;
+                        outcome = scatter_book(sShape[rec.index], sSurf[rec.index], sKind[rec.index], rec.t, ray, colour, u, g);
+                    } else outcome = scatter(sShape[rec.index], sSurf[rec.index], sKind[rec.index], rec.t, ray, colour, u) ? 1 : 0;
+                    if (outcome == 0) nBad++;
+                    else if (outcome == 2) { }
                     else if (pass + 1u >= args.maxDepth) nExhausted++;
                     else {
                         ended = false;

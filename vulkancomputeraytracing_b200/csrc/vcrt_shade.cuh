@@ -115,4 +115,69 @@ VCRT_DEV bool scatter(const float4 shape, const float4 surf, int kind, float t, 
     return false;
 }
 
+// ------------------------------------------------------------------ BOOK semantics (VCRT_SEMANTICS_BOOK)
+// The same path with the reference's matched bugs fixed the way "Ray Tracing in One Weekend" (v4.0.1) writes the routines:
+// face-forwarded normals, uniform-on-the-sphere scatter by rejection sampling, lambertian attenuation = albedo, metal
+// reflects the direction and absorbs below-surface scatter, dielectric with unit directions, Snell and Schlick.
+// Draws: Philox block (pixel, sample, event, attempt); see the oracle's BOOK section for the layout.
+struct BookDraws { uint32_t pixel, sample, event, seedLo, seedHi; };
+
+VCRT_DEV V3 book_unit_vector(const BookDraws& g, const float first[4]) {
+    float u0 = first[0], u1 = first[1], u2 = first[2];
+    for (uint32_t attempt = 0;; attempt++) {
+        V3 p = v3(fsub(fmul(2.f, u0), 1.f), fsub(fmul(2.f, u1), 1.f), fsub(fmul(2.f, u2), 1.f));
+        float lensq = vdot(p, p);
+        if (1e-30f < lensq && lensq <= 1.f) return vdiv(p, fsqrt(lensq));
+        if (attempt == 63u) return v3(1.f, 0.f, 0.f);
+        uint32_t rnd[4];
+        philox4x32_10(g.pixel, g.sample, g.event, attempt + 1u, g.seedLo, g.seedHi, rnd);
+        u0 = u01(rnd[0]); u1 = u01(rnd[1]); u2 = u01(rnd[2]);
+    }
+}
+
+// Returns 0 = unknown material (absorbed + counted), 1 = scattered, 2 = absorbed by the material (metal below the surface).
+VCRT_DEV int scatter_book(const float4 shape, const float4 surf, int kind, float t, Ray& ray, V3& colour, const float u[4], const BookDraws& g) {
+    V3 point = vadd(vscale(ray.d, t), ray.o);
+    V3 outward = vdiv(vsub(point, v3(shape.x, shape.y, shape.z)), shape.w);
+    const bool front_face = vdot(ray.d, outward) < 0.f;                  // hittable.h set_face_normal
+    V3 normal = front_face ? outward : vneg(outward);
+    V3 albedo = v3(surf.x, surf.y, surf.z);
+    if (kind == 1 || kind == 2) {
+        const V3 rv = book_unit_vector(g, u);
+        V3 direction;
+        if (kind == 1) {                                                 // lambertian::scatter
+            direction = vadd(normal, rv);
+            const float s = 1e-8f;
+            if (fabsf(direction.x) < s && fabsf(direction.y) < s && fabsf(direction.z) < s) direction = normal;
+        } else {                                                         // metal::scatter
+            const float fuzz = surf.w < 1.f ? surf.w : 1.f;
+            V3 reflected = vsub(ray.d, vscale(normal, fmul(2.f, vdot(ray.d, normal))));
+            direction = vadd(vunit(reflected), vscale(rv, fuzz));
+        }
+        colour = vmul(colour, albedo);
+        ray.o = point; ray.d = direction;
+        return (kind == 1 || vdot(direction, normal) > 0.f) ? 1 : 2;
+    }
+    if (kind == 3) {                                                     // dielectric::scatter
+        const float ri = front_face ? fdiv(1.0f, surf.w) : surf.w;
+        V3 ud = vunit(ray.d);
+        const float cos_theta = fminf(vdot(vneg(ud), normal), 1.0f);
+        const float sin_theta = fsqrt(fsub(1.0f, fmul(cos_theta, cos_theta)));
+        float r0 = fdiv(fsub(1.f, ri), fadd(1.f, ri));
+        r0 = fmul(r0, r0);
+        const float x = fsub(1.f, cos_theta), x2 = fmul(x, x);
+        const float reflectance = fadd(r0, fmul(fsub(1.f, r0), fmul(fmul(x2, x2), x)));
+        V3 direction;
+        if (fmul(ri, sin_theta) > 1.0f || reflectance > u[3]) direction = vsub(ud, vscale(normal, fmul(2.f, vdot(ud, normal))));
+        else {
+            V3 perp = vscale(vadd(ud, vscale(normal, cos_theta)), ri);
+            V3 parallel = vscale(normal, -fsqrt(fabsf(fsub(1.0f, vdot(perp, perp)))));
+            direction = vadd(perp, parallel);
+        }
+        ray.o = point; ray.d = direction;
+        return 1;
+    }
+    return 0;
+}
+
 }  // namespace vcrt

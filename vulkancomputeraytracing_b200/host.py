@@ -52,12 +52,13 @@ def upload_scene(spheres, camera=None):
 
 
 def render_params(width, height, spp, depth=50, seed=0, sample_offset=0, traversal=cabi.VCRT_TRAVERSAL_AUTO, flags=0,
-                  sample_chunks=0, total_samples=0, shape=0):
+                  sample_chunks=0, total_samples=0, shape=0, semantics=0):
     p = cabi.VcrtRenderParams()
     cabi.load().vcrtDefaultRenderParams(ctypes.byref(p))
     p.width, p.height, p.samplesPerPixel, p.maxDepth, p.seed = width, height, spp, depth, seed
     p.sampleOffset, p.traversal, p.flags, p.sampleChunks, p.totalSamples = sample_offset, traversal, flags, sample_chunks, total_samples
     p.reserved[1] = shape
+    p.semantics = semantics
     return p
 
 

@@ -72,7 +72,13 @@ VkResult FrontendWritePpm(IN const char* path)
     for (uint32_t y = 0; y < frontendImageHeight; y++) {
         const float* source = frontendHostImage + (size_t)y * frontendImageWidth * 4;
         for (uint32_t x = 0; x < frontendImageWidth; x++)
-            for (int c = 0; c < 3; c++) row[3 * x + c] = encodeSrgb(source[4 * x + c]);
+            for (int c = 0; c < 3; c++) {
+                const float value = source[4 * x + c];
+                // BOOK images are already gamma-2 encoded by the layer (the book's linear_to_gamma): quantise only
+                row[3 * x + c] = rendererConfiguration.semantics == VCRT_SEMANTICS_BOOK
+                                     ? (unsigned char)(255.999f * (value > 0.0f ? (value < 0.999f ? value : 0.999f) : 0.0f))
+                                     : encodeSrgb(value);
+            }
         fwrite(row, 1, (size_t)frontendImageWidth * 3, file);
     }
     delete[] row;

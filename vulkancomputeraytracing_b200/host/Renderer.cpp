@@ -99,6 +99,7 @@ VkResult DrawNextFrame(void)
     params.maxDepth = config.maxDepth;
     params.seed = config.seed;
     params.traversal = config.traversal;
+    params.semantics = config.semantics;
     if (config.progressive) {
         // frame k adds sample indices [k*spp, (k+1)*spp) to the running sums; the image is their mean so far
         params.sampleOffset = rendererFrameIndex * config.samplesPerFrame;

@@ -6,7 +6,7 @@
 
     usage: VulkanComputeRayTracing [--width W] [--height H] [--spp N] [--depth D] [--frames F] [--progressive]
                                    [--seed S] [--device I] [--traversal auto|brute|lbvh|simple]
-                                   [--grid G] [--stress] [--scene file.glsl] [--out prefix]
+                                   [--grid G] [--stress] [--book] [--scene file.glsl] [--out prefix]
 */
 #include "../../include/Frontend.hpp"
 #include "../../include/Platform.hpp"
@@ -26,7 +26,7 @@ const char* applicationNameNarrow = "Vulkan Compute Raytracing";
 
 RendererConfiguration rendererConfiguration = {
     .width = WINDOW_WIDTH, .height = WINDOW_HEIGHT, .samplesPerFrame = 1, .maxDepth = 50, .frames = 1, .progressive = 0,
-    .traversal = VCRT_TRAVERSAL_AUTO, .sceneGridHalf = 11, .sceneVariant = VCRT_SCENE_REFERENCE, .seed = 0, .device = 0,
+    .traversal = VCRT_TRAVERSAL_AUTO, .semantics = VCRT_SEMANTICS_REFERENCE, .sceneGridHalf = 11, .sceneVariant = VCRT_SCENE_REFERENCE, .seed = 0, .device = 0,
     .sceneFile = nullptr, .outputPrefix = nullptr,
 };
 
@@ -46,6 +46,7 @@ static int parseArguments(int argc, char** argv)
         else if (!strcmp(flag, "--grid")) ok = number(config.sceneGridHalf);
         else if (!strcmp(flag, "--progressive")) config.progressive = 1;
         else if (!strcmp(flag, "--stress")) config.sceneVariant = VCRT_SCENE_STRESS;
+        else if (!strcmp(flag, "--book")) config.semantics = VCRT_SEMANTICS_BOOK;
         else if (!strcmp(flag, "--seed") && value) { config.seed = strtoull(value, nullptr, 10); i++; }
         else if (!strcmp(flag, "--device") && value) { config.device = atoi(value); i++; }
         else if (!strcmp(flag, "--scene") && value) { config.sceneFile = value; i++; }

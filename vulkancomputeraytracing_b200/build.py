@@ -22,7 +22,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 GXX = "/usr/bin/g++"   # the image's $CXX (/opt/gcc) lacks libgomp.spec; pin the distro compiler
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++20",
-              "-Xcompiler", "-fPIC,-ffp-contract=off", "-ccbin", GXX]
+              "-Xcompiler", "-fPIC,-ffp-contract=off", "-ccbin", GXX] + os.environ.get("VCRT_EXTRA_NVCC", "").split()
 GXX_FLAGS = ["-std=c++20", "-O2", "-ffp-contract=off", "-Wall", "-I", INCLUDE]
 
 

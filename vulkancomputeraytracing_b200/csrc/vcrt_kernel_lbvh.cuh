@@ -52,6 +52,7 @@ VCRT_DEV void hit_ordered(float4 shape, int device, uint32_t orig, const Ray& r,
     float c = fsub(vdot(oc, oc), fmul(shape.w, shape.w));
     float disc = fsub(fmul(half_b, half_b), fmul(a, c));
     if (disc < 0) return;
+    if (half_b > 1e-18f && c >= 0.f) return;   // both roots <= 0 exactly, see hit_exact
     float sqrtd = fsqrt(disc);
     float root = fdiv(fsub(-half_b, sqrtd), a);
     if (root <= kTMin) {   // only then can the far root be the accepted one (it is never smaller than the near root)

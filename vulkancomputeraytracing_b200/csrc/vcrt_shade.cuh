@@ -17,6 +17,11 @@ VCRT_DEV void hit_exact(float4 shape, int index, const Ray& r, float a, HitRec& 
     float c = fsub(vdot(oc, oc), fmul(shape.w, shape.w));
     float disc = fsub(fmul(half_b, half_b), fmul(a, c));
     if (disc < 0) return;
+    // Moving away from a sphere we are not inside (half_b > 0, c >= 0): a*c >= 0 gives disc <= fl(half_b^2), and
+    // sqrt(fl(x*x)) == |x| exactly in round-to-nearest binary arithmetic, so sqrtd <= half_b and both numerators are <= 0:
+    // the reference rejects both roots against t_min.  Same outcome, without the square root and the two divisions
+    // (this is every ray leaving the surface it just scattered from, and every sphere behind the origin).
+    if (half_b > 1e-18f && c >= 0.f) return;   // 1e-18: half_b^2 stays a normal number, which the sqrt identity needs
     float sqrtd = fsqrt(disc);
     float root = fdiv(fsub(-half_b, sqrtd), a);
     if (root <= kTMin || rec.t <= root) {

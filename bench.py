@@ -311,6 +311,15 @@ def run_b200(args):
                          "filter_candidates_per_ray": cand / rays if rays else None},
             "clocks": clocks, "gpu": gpu_name,
         }
+        # roofline.traffic: DRAM bytes of one launch of this kernel on this workload, from a committed ncu --set full capture
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                t = json.load(f).get(line["roofline"]["kernel"], {}).get(name)
+            if t:
+                line["roofline"]["traffic"] = t["dram_bytes_per_launch"]
+                line["roofline"]["traffic_source"] = t["source"]
+        except (OSError, ValueError):
+            pass
         if lbvh is not None:
             lbvh["speedup_vs_headline"] = lbvh["value"] / value
             line["lbvh_same_workload"] = lbvh

@@ -261,9 +261,21 @@ def test_lbvh_duplicates_and_coincident_centres(oracle, vcrt):
         host.destroy()
 
 
-def test_first_generation_scan_kernel_agrees(oracle, gpu_scene):
-    # shape=1 selects the LDS-fed first-generation brute-force kernel (kept for A/B measurements)
-    cpu, cst = oracle.render(gpu_scene, 203, 113, 3)
-    for shape in (1, 0):
-        gpu, st = host.render(203, 113, 3, traversal=BRUTE, sample_chunks=1, shape=shape)
-        assert_same(gpu, st, cpu, cst)
+@pytest.mark.parametrize("shape", [1, 10, 11, 20, 21])
+def test_every_brute_force_kernel_generation_agrees(oracle, vcrt, shape):
+    # development switch `shape`: 1 = first generation (LDS-fed filter), 10 / 11 = uniform-datapath scan (512x4 / 1024x2 rays),
+    # 20 / 21 = warp-compacted shading (1024x2 / 512x4 rays).  Same bits from all of them, in both semantics and accumulators.
+    for scene, cam in ((host.generate_scene(), None), (host.stress_scene(), None)):
+        host.upload_scene(scene, cam)
+        try:
+            cpu, cst = oracle.render(scene, 203, 113, 3, depth=9)
+            gpu, st = host.render(203, 113, 3, depth=9, traversal=BRUTE, sample_chunks=1, shape=shape)
+            assert_same(gpu, st, cpu, cst)
+            fixed, sf = host.render(203, 113, 3, depth=9, traversal=BRUTE, shape=shape)
+            assert sf.rays == cst["rays"] and np.abs(fixed - cpu).max() <= 2.0 ** -22
+            if shape != 1:
+                book, cb = oracle.render_book(scene, 96, 54, 2)
+                gb, sb = host.render(96, 54, 2, traversal=BRUTE, sample_chunks=1, shape=shape, semantics=cabi.VCRT_SEMANTICS_BOOK)
+                assert sb.rays == cb["rays"] and sb.depthExhausted == cb["exhausted"] and np.array_equal(gb, book)
+        finally:
+            host.destroy()

@@ -11,6 +11,7 @@
 #include "vcrt_kernel_scan.cuh"
 #include "vcrt_kernel_lbvh.cuh"
 #include "vcrt_kernel_scanu.cuh"
+#include "vcrt_kernel_scanw.cuh"
 
 #include <cub/device/device_radix_sort.cuh>
 
@@ -160,7 +161,7 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
         kept = 0;
         for (uint32_t i = 0; i < count; i++) if (spheres[i].radius > kAlwaysRadius && kept < kMaxAlways) { order[scanCount + alwaysCount++] = i; kept++; }
     }
-    const uint32_t scanPad = (scanCount + 7u) & ~7u;   // the scan walks the list 8 spheres at a time
+    const uint32_t scanPad = (scanCount + 15u) & ~15u;   // the scan walks the list 16 (first generation: 8) spheres at a time
 
     SceneBlob hdr; memset(&hdr, 0, sizeof hdr);
     hdr.count = count; hdr.scanCount = scanCount; hdr.scanPad = scanPad; hdr.alwaysCount = alwaysCount;
@@ -582,6 +583,24 @@ static int launchScanU(const RenderArgs& args, uint32_t* launches) {
     *launches += 1;
     return VCRT_SUCCESS;
 }
+template <int THREADS, int PAIRS, int LCAP, bool FIXED>
+static int launchScanW(const RenderArgs& args, uint32_t* launches) {
+    using Cfg = ScanWConfig<THREADS, PAIRS, LCAP>;
+    const size_t smem = Cfg::smem_bytes(cudaComputeSceneHeader.bytes);
+    auto kernel = render_scanw_kernel<THREADS, PAIRS, LCAP, FIXED>;
+    CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned int grid = (unsigned int)cudaComputeSmCount;   // persistent: one CTA per SM
+    const unsigned int firstDynamicItem = grid * Cfg::R * THREADS;
+    CUDA_TRY(cudaMemcpyAsync(cudaComputeWorkCounter, &firstDynamicItem, sizeof firstDynamicItem, cudaMemcpyHostToDevice, cudaComputeStream));
+    kernel<<<grid, THREADS, smem, cudaComputeStream>>>(cudaComputeSceneBlob, args, (int)cudaComputeSceneHeader.scanPad);
+    CUDA_TRY(cudaGetLastError());
+    *launches += 1;
+    return VCRT_SUCCESS;
+}
+static bool scanWFits(int threads, int pairs, int lcap) {
+    size_t state = (size_t)WF_COUNT * 2 * pairs * threads * 4, lists = (size_t)lcap * threads * 2, map = (size_t)2 * pairs * threads;
+    return cudaComputeSceneInConstant && 16 + (size_t)cudaComputeSceneHeader.bytes + state + lists + map <= 227 * 1024;
+}
 static bool scanUFits(int threads, int pairs, int lcap) {
     size_t state = (size_t)SF_COUNT * 2 * pairs * threads * 4, lists = (size_t)lcap * threads * 2;
     return cudaComputeSceneInConstant && 16 + (size_t)cudaComputeSceneHeader.bytes + state + lists <= 227 * 1024;
@@ -666,7 +685,9 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         const uint32_t shape = p->reserved[1];
         // default: 1024 threads x 2 rays (32 warps per SM hide the shading phases best; measured 94 ms vs 102 ms for 512 x 4
         // at 1080p x 128 spp), falling back to 512 x 4 and then to the first-generation kernel as shared memory runs out
-        if ((shape == 0 || shape == 11) && scanUFits(1024, 1, 30)) rc = fixedMode ? launchScanU<1024, 1, 30, true>(args, &launches) : launchScanU<1024, 1, 30, false>(args, &launches);
+        if (shape == 20 && scanWFits(1024, 1, 24)) rc = fixedMode ? launchScanW<1024, 1, 24, true>(args, &launches) : launchScanW<1024, 1, 24, false>(args, &launches);
+        else if (shape == 21 && scanWFits(512, 2, 24)) rc = fixedMode ? launchScanW<512, 2, 24, true>(args, &launches) : launchScanW<512, 2, 24, false>(args, &launches);
+        else if ((shape == 0 || shape == 11) && scanUFits(1024, 1, 30)) rc = fixedMode ? launchScanU<1024, 1, 30, true>(args, &launches) : launchScanU<1024, 1, 30, false>(args, &launches);
         else if ((shape == 0 || shape == 10) && scanUFits(512, 2, 30)) rc = fixedMode ? launchScanU<512, 2, 30, true>(args, &launches) : launchScanU<512, 2, 30, false>(args, &launches);
         else if (shape == 12 && fixedMode && scanUFits(256, 4, 30)) rc = launchScanU<256, 4, 30, true>(args, &launches);
         else if (shape == 2 && fixedMode && scanFits(1024, 1, 12)) rc = launchScan<1024, 1, 12, true>(args, &launches);

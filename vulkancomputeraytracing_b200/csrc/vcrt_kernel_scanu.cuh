@@ -50,7 +50,12 @@ struct ScanUConfig {
     static __host__ __device__ size_t smem_bytes(uint32_t blobBytes) { return 16 + (size_t)blobBytes + kStateBytes + kListBytes; }
 };
 
-template <int THREADS, int PAIRS, int LCAP, bool FIXED>
+// m |= bit when q >= s: one compare and one predicated OR (the plain C form costs a select and an add on top of the compare)
+VCRT_DEV void flag_if_ge(uint32_t& m, float q, float s, uint32_t bit) {
+    asm("{\n\t.reg .pred p;\n\tsetp.ge.f32 p, %1, %2;\n\t@p or.b32 %0, %0, %3;\n\t}" : "+r"(m) : "f"(q), "f"(s), "r"(bit));
+}
+
+template <int THREADS, int PAIRS, int LCAP, bool FIXED, int UNROLL = 16>
 __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned char* __restrict__ blobGlobal, RenderArgs args, int scanPad) {
     using Cfg = ScanUConfig<THREADS, PAIRS, LCAP>;
     constexpr int R = Cfg::R;
@@ -164,12 +169,12 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
 #pragma unroll 1
             for (int base = 0; base < scanPad; base += 32) {
                 uint32_t mask = 0u;
-                const int lim = min(32, scanPad - base);   // scanPad is a multiple of 8
+                const int lim = min(32, scanPad - base);   // scanPad is a multiple of 16
 #pragma unroll 1
-                for (int kk = 0; kk < lim; kk += 8) {
-                    uint32_t m8 = 0u;
+                for (int kk = 0; kk < lim; kk += UNROLL) {
+                    uint32_t mEven = 0u, mOdd = 0u;   // two accumulators: half the dependent-OR chain
 #pragma unroll
-                    for (int u = 0; u < 8; u++) {
+                    for (int u = 0; u < UNROLL; u++) {
                         const float4 s = cSceneHot[base + kk + u];
                         const u64 cx = pack2(s.x, s.x), cy = pack2(s.y, s.y), cz = pack2(s.z, s.z);
                         float qmax = -kPosInf;
@@ -181,9 +186,9 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                             float q0, q1; unpack2(q, q0, q1);
                             qmax = fmaxf(qmax, fmaxf(q0, q1));
                         }
-                        if (qmax >= s.w) m8 |= 1u << u;
+                        flag_if_ge(u & 1 ? mOdd : mEven, qmax, s.w, 1u << u);
                     }
-                    mask |= m8 << kk;
+                    mask |= (mEven | mOdd) << kk;
                 }
                 while (mask) {
                     const int k = __ffs(mask) - 1;

@@ -143,7 +143,7 @@ def test_tiny_and_ragged_images(oracle, gpu_scene, traversal, shape):
 @pytest.mark.parametrize("traversal", [BRUTE, SIMPLE, LBVH])
 def test_depth_limits(oracle, gpu_scene, traversal):
     img, st = host.render(32, 18, 2, depth=0, traversal=traversal)     # no pass of functions.glsl:73 runs: black (bug B7)
-    assert (img[..., :3] == 0).all() and (img[..., 3] == 1).all() and st.rays == 0
+    assert (img[..., :3] == 0).all() and (img[..., 3] == 1).all() and st.rays == 0 and st.depthExhausted == st.samples
     for depth in (1, 2):
         cpu, cst = oracle.render(gpu_scene, 64, 36, 2, depth=depth)
         gpu, st = host.render(64, 36, 2, depth=depth, traversal=traversal, sample_chunks=1)
@@ -277,5 +277,40 @@ def test_every_brute_force_kernel_generation_agrees(oracle, vcrt, shape):
                 book, cb = oracle.render_book(scene, 96, 54, 2)
                 gb, sb = host.render(96, 54, 2, traversal=BRUTE, sample_chunks=1, shape=shape, semantics=cabi.VCRT_SEMANTICS_BOOK)
                 assert sb.rays == cb["rays"] and sb.depthExhausted == cb["exhausted"] and np.array_equal(gb, book)
+        finally:
+            host.destroy()
+
+
+@pytest.mark.parametrize("traversal", [BRUTE, SIMPLE, LBVH])
+def test_count_stats_match_oracle(oracle, gpu_scene, traversal):
+    # VCRT_FLAG_COUNT_STATS: hits by material and the path-length histogram (SURVEY.md 8c acceptance test) equal the oracle's
+    cpu, cst = oracle.render(gpu_scene, 160, 90, 4)
+    gpu, st = host.render(160, 90, 4, traversal=traversal, sample_chunks=1, flags=cabi.VCRT_FLAG_COUNT_STATS)
+    assert_same(gpu, st, cpu, cst)
+    assert list(st.hitsByMaterial) == cst["hits"] and list(st.pathLength) == cst["path_hist"]
+    assert sum(st.pathLength) + st.depthExhausted == st.samples
+    frac = np.array(st.hitsByMaterial[1:], float) / sum(st.hitsByMaterial)
+    assert np.allclose(frac, [0.669, 0.199, 0.133], atol=0.02)              # SURVEY.md 3.4 probe
+    plain, sp = host.render(160, 90, 4, traversal=traversal, sample_chunks=1)
+    assert sum(sp.hitsByMaterial) == 0 and np.array_equal(plain, gpu)       # off by default, and never changes the image
+
+
+def test_both_lbvh_kernel_generations_agree(oracle, vcrt):
+    # development switch shape 31: the first-generation LBVH kernel (nested sample / bounce loops); the default is the flat
+    # loop whose idle lanes restart together.  Same bits as the oracle in strict order, same fixed-point image, both semantics.
+    for scene in (host.generate_scene(), host.stress_scene(), host.generate_scene(30)):
+        host.upload_scene(scene)
+        try:
+            for shape in (0, 31):
+                for depth in (9, 1, 0):
+                    cpu, cst = oracle.render(scene, 203, 113, 3, depth=depth)
+                    gpu, st = host.render(203, 113, 3, depth=depth, traversal=LBVH, sample_chunks=1, shape=shape)
+                    assert_same(gpu, st, cpu, cst)
+                book, cb = oracle.render_book(scene, 96, 54, 2)
+                gb, sb = host.render(96, 54, 2, traversal=LBVH, sample_chunks=1, shape=shape, semantics=cabi.VCRT_SEMANTICS_BOOK)
+                assert sb.rays == cb["rays"] and sb.depthExhausted == cb["exhausted"] and np.array_equal(gb, book)
+            nested, sn = host.render(203, 113, 5, traversal=LBVH, shape=31)
+            flat, sf = host.render(203, 113, 5, traversal=LBVH)
+            assert sf.rays == sn.rays and sf.nodeVisits == sn.nodeVisits and np.array_equal(flat, nested)
         finally:
             host.destroy()

@@ -24,6 +24,8 @@
 
 using namespace vcrt;
 
+static_assert(kFlagCountStats == VCRT_FLAG_COUNT_STATS, "device-side copy of the flag bit");
+
 // ------------------------------------------------------------------ file-static state
 // (reference Renderer.cpp:13-33 keeps its pipeline, image and memory handles the same way)
 static int cudaComputeDevice = 0;
@@ -539,9 +541,9 @@ static int ensureBvh(void) {
     return VCRT_SUCCESS;
 }
 
-template <bool FIXED>
+template <bool FIXED, bool STATS, bool FLAT>
 static int launchLbvh(const RenderArgs& args, uint32_t* launches) {
-    auto kernel = render_lbvh_kernel<FIXED>;
+    auto kernel = FLAT ? render_lbvh_flat_kernel<FIXED, STATS> : render_lbvh_kernel<FIXED, STATS>;
     int perSm = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, 256, 0));
     if (perSm < 1) perSm = 1;
@@ -678,7 +680,12 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         CUDA_TRY(cudaGetLastError());
         launches++;
     } else if (traversal == VCRT_TRAVERSAL_LBVH) {
-        rc = fixedMode ? launchLbvh<true>(args, &launches) : launchLbvh<false>(args, &launches);
+        const bool flat = p->reserved[1] != 31;   // experiment switch: 31 = the first-generation nested-loop kernel
+        const bool stats = (args.flags & kFlagCountStats) != 0;
+        if (flat) rc = stats ? (fixedMode ? launchLbvh<true, true, true>(args, &launches) : launchLbvh<false, true, true>(args, &launches))
+                             : (fixedMode ? launchLbvh<true, false, true>(args, &launches) : launchLbvh<false, false, true>(args, &launches));
+        else rc = stats ? (fixedMode ? launchLbvh<true, true, false>(args, &launches) : launchLbvh<false, true, false>(args, &launches))
+                        : (fixedMode ? launchLbvh<true, false, false>(args, &launches) : launchLbvh<false, false, false>(args, &launches));
         if (rc) return rc;
     } else {
         // reserved[1]: experiment switch for the CTA shape (0 = default)
@@ -739,6 +746,7 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     VcrtRenderStats& st = cudaComputeLastStats; memset(&st, 0, sizeof st);
     st.samples = (uint64_t)pixels * p->samplesPerPixel;
     st.rays = ctr[CTR_RAYS]; st.depthExhausted = ctr[CTR_EXHAUSTED]; st.badMaterial = ctr[CTR_BAD_MATERIAL];
+    if (p->maxDepth == 0) st.depthExhausted = st.samples;   // no kernel ran: every sample ends at the (zero) depth limit
     st.candidates = ctr[CTR_CANDIDATES]; st.listOverflows = ctr[CTR_OVERFLOWS];
     st.sphereTests = traversal == VCRT_TRAVERSAL_LBVH ? ctr[CTR_TESTS] : st.rays * cudaComputeSceneHeader.count; st.nodeVisits = ctr[CTR_NODES];
     for (int i = 0; i < 4; i++) st.hitsByMaterial[i] = ctr[CTR_HITS0 + i];

@@ -110,6 +110,8 @@ struct RenderArgs {
 enum Counter { CTR_RAYS = 0, CTR_EXHAUSTED, CTR_BAD_MATERIAL, CTR_CANDIDATES, CTR_OVERFLOWS, CTR_TESTS, CTR_NODES,
                CTR_HITS0, CTR_HITS1, CTR_HITS2, CTR_HITS3, CTR_PATH0, CTR_COUNT = CTR_PATH0 + 8 };
 
+constexpr uint32_t kFlagCountStats = 1u << 3;   // VCRT_FLAG_COUNT_STATS of include/vcrt.h
+
 struct Ray { V3 o, d; };
 struct HitRec { float t; int index; };  // nearest accepted root and its sphere (index < 0: none)
 

@@ -43,6 +43,10 @@ struct BvhScene {
     float radiusMin, radiusMax;   // over the tree spheres
 };
 
+#ifndef LBVH_BLOCKS
+#define LBVH_BLOCKS 4   // resident CTAs of 256 per SM the register budget is set for (64 registers; measured 1.4 % faster than 3)
+#endif
+
 struct OrderedHit { float t; int device; uint32_t orig; };
 
 // Candidate root of one sphere, independent of what was found before (see the file header).
@@ -63,8 +67,9 @@ VCRT_DEV void hit_ordered(float4 shape, int device, uint32_t orig, const Ray& r,
     rec.t = root; rec.device = device; rec.orig = orig;
 }
 
-template <bool FIXED>
-__global__ void __launch_bounds__(256, 3) render_lbvh_kernel(BvhScene scene, RenderArgs args) {
+// STATS: the VCRT_FLAG_COUNT_STATS counters are a compile-time variant here (a run-time test costs this kernel 2 %)
+template <bool FIXED, bool STATS>
+__global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_kernel(BvhScene scene, RenderArgs args) {
     const uint32_t pixels = args.width * args.height;
     const uint32_t sppPerChunk = FIXED ? args.samplesPerItem : (args.spp + args.chunks - 1u) / args.chunks;
     const uint32_t runsPerPixel = (args.spp + sppPerChunk - 1u) / sppPerChunk;
@@ -164,7 +169,11 @@ __global__ void __launch_bounds__(256, 3) render_lbvh_kernel(BvhScene scene, Ren
                         }
                     }
                 }
-                if (rec.device < 0) { result = vmul(colour, sky(ray.d)); finished = true; break; }
+                if (rec.device < 0) {
+                    if constexpr (STATS) atomicAdd(&args.counters[CTR_PATH0 + min(pass, 7u)], 1ull);
+                    result = vmul(colour, sky(ray.d)); finished = true; break;
+                }
+                if constexpr (STATS) { const int k = __ldg(&scene.kind[rec.device]); atomicAdd(&args.counters[CTR_HITS0 + ((k >= 1 && k <= 3) ? k : 0)], 1ull); }
                 philox4x32_10(pixel, sample, pass + 1u, 0u, args.seedLo, args.seedHi, rnd);
                 float u[4] = {u01(rnd[0]), u01(rnd[1]), u01(rnd[2]), u01(rnd[3])};
                 int outcome;   // 0 = unknown material, 1 = scattered, 2 = absorbed by the material (BOOK metal)
@@ -186,6 +195,220 @@ __global__ void __launch_bounds__(256, 3) render_lbvh_kernel(BvhScene scene, Ren
     }
     // one atomic per warp per counter
     unsigned long long wRays = nRays, wNodes = nNodes, wTests = nTests;
+    for (int off = 16; off > 0; off >>= 1) {
+        wRays += __shfl_down_sync(0xffffffffu, wRays, off); wNodes += __shfl_down_sync(0xffffffffu, wNodes, off);
+        wTests += __shfl_down_sync(0xffffffffu, wTests, off);
+        nExhausted += __shfl_down_sync(0xffffffffu, nExhausted, off); nBad += __shfl_down_sync(0xffffffffu, nBad, off);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&args.counters[CTR_RAYS], wRays); atomicAdd(&args.counters[CTR_NODES], wNodes); atomicAdd(&args.counters[CTR_TESTS], wTests);
+        if (nExhausted) atomicAdd(&args.counters[CTR_EXHAUSTED], (unsigned long long)nExhausted);
+        if (nBad) atomicAdd(&args.counters[CTR_BAD_MATERIAL], (unsigned long long)nBad);
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// Second generation: the same path tracer as ONE flat loop per thread.  Every trip of the loop traces
+// exactly one ray per lane; a lane whose path has ended (sky, absorbed, depth) starts its next sample
+// (or takes the next work item) in the same trip instead of idling until the longest path of its warp
+// is done.  The image cannot change: a path's arithmetic is the same sequence of operations, samples
+// of one run are still summed in order by the thread that owns the run (strict mode), and the
+// fixed-point sums do not depend on the order at all.
+#ifndef LBVH_REFILL
+#define LBVH_REFILL 16   // 32 = an idle lane restarts at once; 16 measured best
+#endif
+#ifndef LBVH_WHILE
+#define LBVH_WHILE 0
+#endif
+
+struct LbvhCounts { uint32_t rays, nodes, tests, exhausted, bad; };
+
+VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, OrderedHit& rec, int* stack, LbvhCounts& n) {
+    const float oo = fmaf(ray.o.x, ray.o.x, fmaf(ray.o.y, ray.o.y, ray.o.z * ray.o.z));
+    const bool degenerate = !(a > 1e-30f && a < 1e30f && oo < 1e30f);
+    if (degenerate) {   // the reference's in-order scan, literally (see render_lbvh_kernel)
+        HitRec h; h.t = kTMax; h.index = -1;
+        uint32_t i = 0, j = scene.treeCount;
+        while (i < scene.treeCount || j < scene.count) {
+            const bool takeTree = j >= scene.count || (i < scene.treeCount && scene.origIndex[i] < scene.origIndex[j]);
+            const uint32_t k = takeTree ? i++ : j++;
+            hit_exact(scene.shape[k], (int)k, ray, a, h);
+            n.tests++;
+        }
+        rec.t = h.t; rec.device = h.index;
+        return;
+    }
+    for (uint32_t k = scene.treeCount; k < scene.count; k++) { hit_ordered(__ldg(&scene.shape[k]), (int)k, __ldg(&scene.origIndex[k]), ray, a, rec); n.tests++; }
+    if (scene.treeCount == 1u) { hit_ordered(__ldg(&scene.leafShape[0]), (int)__ldg(&scene.leafDevice[0]), __ldg(&scene.leafOrig[0]), ray, a, rec); n.tests++; }
+    if (scene.treeCount <= 1u) return;
+    // per-ray widening of every box and the slab constants: as in render_lbvh_kernel
+    const float fx = fmaxf(fabsf(ray.o.x - scene.centreMin.x), fabsf(ray.o.x - scene.centreMax.x));
+    const float fy = fmaxf(fabsf(ray.o.y - scene.centreMin.y), fabsf(ray.o.y - scene.centreMax.y));
+    const float fz = fmaxf(fabsf(ray.o.z - scene.centreMin.z), fabsf(ray.o.z - scene.centreMax.z));
+    const float F2 = fmaf(fx, fx, fmaf(fy, fy, fz * fz));
+    const float K = 3.814697265625e-06f * (F2 + scene.radiusMax * scene.radiusMax);
+    const float grow = fminf(sqrtf(K), K / (2.f * scene.radiusMin)) * 1.0001f + 9.5367431640625e-07f * (sqrtf(oo) + sqrtf(F2));
+    const bool px_ = ray.d.x >= 0.f, py_ = ray.d.y >= 0.f, pz_ = ray.d.z >= 0.f;
+    const bool ux = fabsf(ray.d.x) > 1e-30f, uy = fabsf(ray.d.y) > 1e-30f, uz = fabsf(ray.d.z) > 1e-30f;
+    const float ix = ux ? 1.0f / ray.d.x : 0.f, iy = uy ? 1.0f / ray.d.y : 0.f, iz = uz ? 1.0f / ray.d.z : 0.f;
+    const float kInf = __int_as_float(0x7f800000);
+    const float bnx = ux ? fmaf(-ray.o.x, ix, -grow * fabsf(ix)) : -kInf, bfx = ux ? fmaf(-ray.o.x, ix, grow * fabsf(ix)) : kInf;
+    const float bny = uy ? fmaf(-ray.o.y, iy, -grow * fabsf(iy)) : -kInf, bfy = uy ? fmaf(-ray.o.y, iy, grow * fabsf(iy)) : kInf;
+    const float bnz = uz ? fmaf(-ray.o.z, iz, -grow * fabsf(iz)) : -kInf, bfz = uz ? fmaf(-ray.o.z, iz, grow * fabsf(iz)) : kInf;
+#if LBVH_WHILE
+    // while-while: a warp first walks inner nodes until every lane holds a leaf (or is done), then tests the leaves together
+    constexpr int kDone = (int)0x80000000;   // = ~0x7fffffff, never a leaf
+    stack[0] = kDone;
+    int sp = 1, node = 0;
+    for (;;) {
+        while (node >= 0) {
+            n.nodes++;
+            const float4 na = __ldg(&scene.nodes[node].a), nb = __ldg(&scene.nodes[node].b), nc = __ldg(&scene.nodes[node].c);
+            const int2 ch = __ldg(reinterpret_cast<const int2*>(&scene.nodes[node].child0));
+            const float n0 = fmaxf(fmaxf(fmaf(px_ ? na.x : na.w, ix, bnx), fmaf(py_ ? na.y : nb.x, iy, bny)), fmaf(pz_ ? na.z : nb.y, iz, bnz));
+            const float f0 = fminf(fminf(fmaf(px_ ? na.w : na.x, ix, bfx), fmaf(py_ ? nb.x : na.y, iy, bfy)), fmaf(pz_ ? nb.y : na.z, iz, bfz));
+            const float n1 = fmaxf(fmaxf(fmaf(px_ ? nb.z : nc.y, ix, bnx), fmaf(py_ ? nb.w : nc.z, iy, bny)), fmaf(pz_ ? nc.x : nc.w, iz, bnz));
+            const float f1 = fminf(fminf(fmaf(px_ ? nc.y : nb.z, ix, bfx), fmaf(py_ ? nc.z : nb.w, iy, bfy)), fmaf(pz_ ? nc.w : nc.x, iz, bfz));
+            const bool h0 = !(n0 > f0) && !(f0 < 0.f) && !(n0 > rec.t);   // written so that a NaN bound passes
+            const bool h1 = !(n1 > f1) && !(f1 < 0.f) && !(n1 > rec.t);
+            if (h0 && h1) {
+                const bool swap = n1 < n0;
+                node = swap ? ch.y : ch.x;
+                stack[sp++] = swap ? ch.x : ch.y;
+            } else if (h0 || h1) node = h0 ? ch.x : ch.y;
+            else node = stack[--sp];
+        }
+        if (node == kDone) break;
+        const int l = ~node;
+        hit_ordered(__ldg(&scene.leafShape[l]), (int)__ldg(&scene.leafDevice[l]), __ldg(&scene.leafOrig[l]), ray, a, rec);
+        n.tests++;
+        node = stack[--sp];
+    }
+}
+#else
+    int sp = 0, node = 0;
+    for (;;) {
+        if (node >= 0) {
+            n.nodes++;
+            const float4 na = __ldg(&scene.nodes[node].a), nb = __ldg(&scene.nodes[node].b), nc = __ldg(&scene.nodes[node].c);
+            const int2 ch = __ldg(reinterpret_cast<const int2*>(&scene.nodes[node].child0));
+            const float n0 = fmaxf(fmaxf(fmaf(px_ ? na.x : na.w, ix, bnx), fmaf(py_ ? na.y : nb.x, iy, bny)), fmaf(pz_ ? na.z : nb.y, iz, bnz));
+            const float f0 = fminf(fminf(fmaf(px_ ? na.w : na.x, ix, bfx), fmaf(py_ ? nb.x : na.y, iy, bfy)), fmaf(pz_ ? nb.y : na.z, iz, bfz));
+            const float n1 = fmaxf(fmaxf(fmaf(px_ ? nb.z : nc.y, ix, bnx), fmaf(py_ ? nb.w : nc.z, iy, bny)), fmaf(pz_ ? nc.x : nc.w, iz, bnz));
+            const float f1 = fminf(fminf(fmaf(px_ ? nc.y : nb.z, ix, bfx), fmaf(py_ ? nc.z : nb.w, iy, bfy)), fmaf(pz_ ? nc.w : nc.x, iz, bfz));
+            const bool h0 = !(n0 > f0) && !(f0 < 0.f) && !(n0 > rec.t);   // written so that a NaN bound passes
+            const bool h1 = !(n1 > f1) && !(f1 < 0.f) && !(n1 > rec.t);
+            if (h0 && h1) {
+                const bool swap = n1 < n0;
+                node = swap ? ch.y : ch.x;
+                stack[sp++] = swap ? ch.x : ch.y;
+                continue;
+            }
+            if (h0 || h1) { node = h0 ? ch.x : ch.y; continue; }
+        } else {
+            const int l = ~node;
+            hit_ordered(__ldg(&scene.leafShape[l]), (int)__ldg(&scene.leafDevice[l]), __ldg(&scene.leafOrig[l]), ray, a, rec);
+            n.tests++;
+        }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+}
+#endif
+
+template <bool FIXED, bool STATS>
+__global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhScene scene, RenderArgs args) {
+    const uint32_t pixels = args.width * args.height;
+    const uint32_t sppPerChunk = FIXED ? args.samplesPerItem : (args.spp + args.chunks - 1u) / args.chunks;
+    const uint32_t runsPerPixel = (args.spp + sppPerChunk - 1u) / sppPerChunk;
+    const uint32_t tilesX = (args.width + 7u) / 8u, tilesY = (args.height + 3u) / 4u, pixelsPadded = tilesX * tilesY * 32u;
+    const uint32_t totalItems = pixelsPadded * runsPerPixel;
+    LbvhCounts n = {0u, 0u, 0u, 0u, 0u};
+    int stack[65];
+
+    const uint32_t firstDynamic = gridDim.x * blockDim.x;
+    uint32_t item = blockIdx.x * blockDim.x + threadIdx.x;
+    bool firstItem = true, haveRun = false;
+    uint32_t s = 0, s1 = 0, pixel = 0, px = 0, py = 0, chunk = 0;   // the run this thread owns
+    uint32_t sample = 0, pass = 0;                                   // the path in flight
+    Ray ray; ray.o = v3(0.f, 0.f, 0.f); ray.d = ray.o;
+    V3 colour = v3(1.f, 1.f, 1.f), sum = v3(0.f, 0.f, 0.f);
+    bool inFlight = false;
+
+    bool drained = false;
+    for (;;) {
+        // idle lanes restart together once fewer than LBVH_REFILL lanes of the warp are still tracing
+        const unsigned flying = __ballot_sync(0xffffffffu, inFlight);
+        if (!inFlight && !drained && __popc(flying) < LBVH_REFILL) {   // start the next sample of the run, or take the next run
+            for (;;) {
+                if (haveRun && s < s1) break;
+                if (haveRun) {
+                    if (!FIXED) args.sums[(size_t)chunk * pixels + pixel] = make_float4(sum.x, sum.y, sum.z, 0.f);
+                    haveRun = false;
+                }
+                if (!firstItem) item = firstDynamic + atomicAdd(args.workCounter, 1u);
+                firstItem = false;
+                if (item >= totalItems) break;
+                chunk = item / pixelsPadded;
+                const uint32_t pid = item - chunk * pixelsPadded;
+                const uint32_t tile = pid >> 5, within = pid & 31u, ty = tile / tilesX, tx = tile - ty * tilesX;
+                px = tx * 8u + (within & 7u); py = ty * 4u + (within >> 3);
+                if (px >= args.width || py >= args.height) continue;
+                s = chunk * sppPerChunk; s1 = min(args.spp, s + sppPerChunk);
+                if (s >= s1) continue;
+                pixel = py * args.width + px;
+                sum = v3(0.f, 0.f, 0.f);
+                haveRun = true;
+                if (args.maxDepth == 0u) { n.exhausted += s1 - s; s = s1; }   // no ray at all: every sample is black
+            }
+            if (!haveRun) drained = true;   // the dispenser is empty: this lane is done
+            else {
+                sample = args.sampleOffset + s; s++;
+                uint32_t rnd[4];
+                philox4x32_10(pixel, sample, 0u, 0u, args.seedLo, args.seedHi, rnd);
+                ray = primary_ray(args.frame, px, py, u01(rnd[0]), u01(rnd[1]));
+                colour = v3(1.f, 1.f, 1.f);
+                pass = 0u;
+                inFlight = true;
+            }
+        }
+        if (!__any_sync(0xffffffffu, inFlight)) break;   // nothing in flight after a refill attempt: every lane is drained
+        if (!inFlight) continue;
+        // one ray
+        n.rays++;
+        const float a = vdot(ray.d, ray.d);
+        OrderedHit rec; rec.t = kTMax; rec.device = -1; rec.orig = 0xffffffffu;
+        lbvh_nearest(scene, ray, a, rec, stack, n);
+        V3 result = v3(0.f, 0.f, 0.f);
+        if (rec.device < 0) {
+            if constexpr (STATS) atomicAdd(&args.counters[CTR_PATH0 + min(pass, 7u)], 1ull);
+            result = vmul(colour, sky(ray.d));
+            inFlight = false;
+        } else {
+            if constexpr (STATS) { const int k = __ldg(&scene.kind[rec.device]); atomicAdd(&args.counters[CTR_HITS0 + ((k >= 1 && k <= 3) ? k : 0)], 1ull); }
+            uint32_t rnd[4];
+            philox4x32_10(pixel, sample, pass + 1u, 0u, args.seedLo, args.seedHi, rnd);
+            float u[4] = {u01(rnd[0]), u01(rnd[1]), u01(rnd[2]), u01(rnd[3])};
+            int outcome;   // 0 = unknown material, 1 = scattered, 2 = absorbed by the material (BOOK metal)
+            if (args.semantics) {
+                BookDraws g; g.pixel = pixel; g.sample = sample; g.event = pass + 1u; g.seedLo = args.seedLo; g.seedHi = args.seedHi;
+                outcome = scatter_book(__ldg(&scene.shape[rec.device]), __ldg(&scene.surf[rec.device]), __ldg(&scene.kind[rec.device]), rec.t, ray, colour, u, g);
+            } else outcome = scatter(__ldg(&scene.shape[rec.device]), __ldg(&scene.surf[rec.device]), __ldg(&scene.kind[rec.device]), rec.t, ray, colour, u) ? 1 : 0;
+            if (outcome != 1) { if (outcome == 0) n.bad++; inFlight = false; }
+            else if (++pass >= args.maxDepth) { n.exhausted++; inFlight = false; }
+        }
+        if (!inFlight) {
+            if (FIXED) {
+                long long* acc = args.fixedSums + 4 * (size_t)pixel;
+                if (result.x != 0.f) atomicAdd((unsigned long long*)acc + 0, (unsigned long long)__float2ll_rn(result.x * kFixedOne));
+                if (result.y != 0.f) atomicAdd((unsigned long long*)acc + 1, (unsigned long long)__float2ll_rn(result.y * kFixedOne));
+                if (result.z != 0.f) atomicAdd((unsigned long long*)acc + 2, (unsigned long long)__float2ll_rn(result.z * kFixedOne));
+            } else sum = vadd(sum, result);
+        }
+    }
+    unsigned long long wRays = n.rays, wNodes = n.nodes, wTests = n.tests;
+    uint32_t nExhausted = n.exhausted, nBad = n.bad;
     for (int off = 16; off > 0; off >>= 1) {
         wRays += __shfl_down_sync(0xffffffffu, wRays, off); wNodes += __shfl_down_sync(0xffffffffu, wNodes, off);
         wTests += __shfl_down_sync(0xffffffffu, wTests, off);

@@ -301,9 +301,12 @@ __global__ void __launch_bounds__(THREADS, 1) render_scan_kernel(const unsigned 
                 V3 colour = v3(STF(SF_CR, r), STF(SF_CG, r), STF(SF_CB, r));
                 V3 result = v3(0.f, 0.f, 0.f);   // black: bug B7 (depth exhausted) and absorbed bad materials
                 bool ended = true;
-                if (rec.index < 0) result = vmul(colour, sky(ray.d));
-                else {
+                if (rec.index < 0) {
+                    if (args.flags & kFlagCountStats) atomicAdd(&args.counters[CTR_PATH0 + min(ST(SF_PASS, r), 7u)], 1ull);
+                    result = vmul(colour, sky(ray.d));
+                } else {
                     const uint32_t pass = ST(SF_PASS, r);
+                    if (args.flags & kFlagCountStats) { const int k = sKind[rec.index]; atomicAdd(&args.counters[CTR_HITS0 + ((k >= 1 && k <= 3) ? k : 0)], 1ull); }
                     uint32_t rnd[4];
                     philox4x32_10(pixel, args.sampleOffset + ST(SF_SAMPLE, r), pass + 1u, 0u, args.seedLo, args.seedHi, rnd);
                     float u[4] = {u01(rnd[0]), u01(rnd[1]), u01(rnd[2]), u01(rnd[3])};

@@ -214,9 +214,12 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanw_kernel(const unsigned
                 }
                 WS(WF_HITT, r, tid) = __float_as_uint(rec.t);
                 WS(WF_HITI, r, tid) = (uint32_t)rec.index;
-                if (rec.index < 0) cat = CAT_MISS;
-                else {
+                if (rec.index < 0) {
+                    cat = CAT_MISS;
+                    if (args.flags & kFlagCountStats) atomicAdd(&args.counters[CTR_PATH0 + min(WS(WF_PASS, r, tid), 7u)], 1ull);
+                } else {
                     const int kind = sKind[rec.index];
+                    if (args.flags & kFlagCountStats) atomicAdd(&args.counters[CTR_HITS0 + ((kind >= 1 && kind <= 3) ? kind : 0)], 1ull);
                     cat = (kind == 1 || kind == 2) ? CAT_HIT_LM : (kind == 3 ? CAT_HIT_GLASS : CAT_BAD);
                     if (cat == CAT_BAD) nBad++;
                 }

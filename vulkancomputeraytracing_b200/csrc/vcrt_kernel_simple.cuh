@@ -31,7 +31,11 @@ __global__ void __launch_bounds__(128) render_simple_kernel(DeviceScene scene, R
                 HitRec rec; rec.t = kTMax; rec.index = -1;
                 const float a = vdot(ray.d, ray.d);
                 for (int i = 0; i < scene.count; i++) hit_exact(__ldg(&scene.shape[i]), i, ray, a, rec);
-                if (rec.index < 0) { result = vmul(colour, sky(ray.d)); finished = true; break; }
+                if (rec.index < 0) {
+                    if (args.flags & kFlagCountStats) atomicAdd(&args.counters[CTR_PATH0 + min(pass, 7u)], 1ull);
+                    result = vmul(colour, sky(ray.d)); finished = true; break;
+                }
+                if (args.flags & kFlagCountStats) { const int k = __ldg(&scene.kind[rec.index]); atomicAdd(&args.counters[CTR_HITS0 + ((k >= 1 && k <= 3) ? k : 0)], 1ull); }
                 philox4x32_10(pixel, sample, pass + 1u, 0u, args.seedLo, args.seedHi, rnd);
                 float u[4] = {u01(rnd[0]), u01(rnd[1]), u01(rnd[2]), u01(rnd[3])};
                 int outcome;   // 0 = unknown material, 1 = scattered, 2 = absorbed by the material (BOOK metal)

@@ -492,6 +492,7 @@ static int ensureBvh(void) {
     const SceneExtent& e = cudaComputeSceneExtent;
     bs.centreMin = make_float3(e.centreMin[0], e.centreMin[1], e.centreMin[2]); bs.centreMax = make_float3(e.centreMax[0], e.centreMax[1], e.centreMax[2]);
     bs.radiusMin = e.radiusMin; bs.radiusMax = e.radiusMax;
+    bs.halfInvRadiusMin = nextafterf(0.5f / e.radiusMin, INFINITY);
     if (n == 0) { cudaComputeBvhReady = true; return VCRT_SUCCESS; }
     size_t sortBytes = 0;
     CUDA_TRY(cub::DeviceRadixSort::SortKeys(nullptr, sortBytes, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)n, 0, 64, cudaComputeStream));
@@ -503,6 +504,7 @@ static int ensureBvh(void) {
     const size_t offLeafOrig = off; off += alignUp(sizeof(uint32_t) * n);
     const size_t offLeafDevice = off; off += alignUp(sizeof(uint32_t) * n);
     const size_t offNodes = off; off += alignUp(sizeof(BvhNode) * nodes);
+    const size_t offOctNodes = off; off += alignUp(sizeof(BvhNode) * nodes * 8);
     const size_t offParent = off; off += alignUp(sizeof(int) * (2 * (size_t)n));
     const size_t offBounds = off; off += alignUp(sizeof(float) * 6 * (2 * (size_t)n));
     const size_t offArrivals = off; off += alignUp(sizeof(unsigned int) * nodes);
@@ -522,7 +524,7 @@ static int ensureBvh(void) {
     unsigned long long* keysIn = (unsigned long long*)(arena + offKeysIn);
     g.keys = keysIn;
     g.leafShape = (float4*)(arena + offLeafShape); g.leafOrig = (uint32_t*)(arena + offLeafOrig); g.leafDevice = (uint32_t*)(arena + offLeafDevice);
-    g.nodes = (BvhNode*)(arena + offNodes); g.parent = (int*)(arena + offParent); g.bounds = (float*)(arena + offBounds);
+    g.nodes = (BvhNode*)(arena + offNodes); g.octNodes = (BvhNode*)(arena + offOctNodes); g.parent = (int*)(arena + offParent); g.bounds = (float*)(arena + offBounds);
     g.arrivals = (unsigned int*)(arena + offArrivals);
     const unsigned int blocks = (n + 255) / 256;
     lbvh_keys_kernel<<<blocks, 256, 0, cudaComputeStream>>>(g);
@@ -536,7 +538,7 @@ static int ensureBvh(void) {
     }
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaStreamSynchronize(cudaComputeStream));
-    bs.nodes = g.nodes; bs.leafShape = g.leafShape; bs.leafOrig = g.leafOrig; bs.leafDevice = g.leafDevice;
+    bs.nodes = g.nodes; bs.octNodes = g.octNodes; bs.leafShape = g.leafShape; bs.leafOrig = g.leafOrig; bs.leafDevice = g.leafDevice;
     cudaComputeBvhReady = true;
     return VCRT_SUCCESS;
 }

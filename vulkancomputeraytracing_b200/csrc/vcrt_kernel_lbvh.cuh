@@ -30,6 +30,7 @@ namespace vcrt {
 
 struct BvhScene {
     const BvhNode* nodes;
+    const BvhNode* octNodes;      // [8][treeCount-1]: the same tree with near / far planes pre-selected per direction octant
     const float4* leafShape;      // sorted order
     const uint32_t* leafOrig;
     const uint32_t* leafDevice;
@@ -41,6 +42,7 @@ struct BvhScene {
     uint32_t count;               // all spheres; [treeCount, count) are tested for every ray
     float3 centreMin, centreMax;  // bounding box of the tree spheres' centres
     float radiusMin, radiusMax;   // over the tree spheres
+    float halfInvRadiusMin;       // >= 1 / (2 radiusMin), rounded up
 };
 
 #ifndef LBVH_BLOCKS
@@ -221,6 +223,12 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_kernel(BvhScene 
 #ifndef LBVH_WHILE
 #define LBVH_WHILE 0
 #endif
+#ifndef LBVH_OCT
+#define LBVH_OCT 1
+#endif
+
+VCRT_DEV float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+VCRT_DEV float sqrt_approx(float x) { float r; asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
 struct LbvhCounts { uint32_t rays, nodes, tests, exhausted, bad; };
 
@@ -248,15 +256,52 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
     const float fz = fmaxf(fabsf(ray.o.z - scene.centreMin.z), fabsf(ray.o.z - scene.centreMax.z));
     const float F2 = fmaf(fx, fx, fmaf(fy, fy, fz * fz));
     const float K = 3.814697265625e-06f * (F2 + scene.radiusMax * scene.radiusMax);
-    const float grow = fminf(sqrtf(K), K / (2.f * scene.radiusMin)) * 1.0001f + 9.5367431640625e-07f * (sqrtf(oo) + sqrtf(F2));
+    // the bound only has to be conservative, so it is built from the approximate unit's sqrt / rcp (relative error <= 2^-22,
+    // against a 1e-4 safety factor on the whole and a slab allowance of 16 eps where ~5 eps are needed, see the file header)
+    const float grow = (fminf(sqrt_approx(K), K * scene.halfInvRadiusMin) + 9.5367431640625e-07f * (sqrt_approx(oo) + sqrt_approx(F2))) * 1.0001f;
     const bool px_ = ray.d.x >= 0.f, py_ = ray.d.y >= 0.f, pz_ = ray.d.z >= 0.f;
     const bool ux = fabsf(ray.d.x) > 1e-30f, uy = fabsf(ray.d.y) > 1e-30f, uz = fabsf(ray.d.z) > 1e-30f;
-    const float ix = ux ? 1.0f / ray.d.x : 0.f, iy = uy ? 1.0f / ray.d.y : 0.f, iz = uz ? 1.0f / ray.d.z : 0.f;
+    const float ix = ux ? rcp_approx(ray.d.x) : 0.f, iy = uy ? rcp_approx(ray.d.y) : 0.f, iz = uz ? rcp_approx(ray.d.z) : 0.f;
     const float kInf = __int_as_float(0x7f800000);
     const float bnx = ux ? fmaf(-ray.o.x, ix, -grow * fabsf(ix)) : -kInf, bfx = ux ? fmaf(-ray.o.x, ix, grow * fabsf(ix)) : kInf;
     const float bny = uy ? fmaf(-ray.o.y, iy, -grow * fabsf(iy)) : -kInf, bfy = uy ? fmaf(-ray.o.y, iy, grow * fabsf(iy)) : kInf;
     const float bnz = uz ? fmaf(-ray.o.z, iz, -grow * fabsf(iz)) : -kInf, bfz = uz ? fmaf(-ray.o.z, iz, grow * fabsf(iz)) : kInf;
-#if LBVH_WHILE
+#if LBVH_OCT
+    // planes picked once per ray: the octant's copy of the node array (vcrt_lbvh.cuh)
+    const uint32_t octant = (px_ ? 0u : 1u) | (py_ ? 0u : 2u) | (pz_ ? 0u : 4u);
+    uint32_t first = octant * (scene.treeCount - 1u);   // 8 (count - 1) < 2^32: the ABI caps a scene far below that
+    asm volatile("" : "+r"(first));                      // keep it in a register: recomputing it per visit costs 8 instructions
+    const BvhNode* nodes = scene.octNodes;
+    int sp = 0, node = 0;
+    for (;;) {
+        if (node >= 0) {
+            n.nodes++;
+            const float4 na = __ldg(&nodes[first + (uint32_t)node].a), nb = __ldg(&nodes[first + (uint32_t)node].b), nc = __ldg(&nodes[first + (uint32_t)node].c);
+            const int2 ch = __ldg(reinterpret_cast<const int2*>(&nodes[first + (uint32_t)node].child0));
+            // child0: near (na.x, na.y, na.z) far (na.w, nb.x, nb.y); child1: near (nb.z, nb.w, nc.x) far (nc.y, nc.z, nc.w)
+            const float n0 = fmaxf(fmaxf(fmaf(na.x, ix, bnx), fmaf(na.y, iy, bny)), fmaf(na.z, iz, bnz));
+            const float f0 = fminf(fminf(fmaf(na.w, ix, bfx), fmaf(nb.x, iy, bfy)), fmaf(nb.y, iz, bfz));
+            const float n1 = fmaxf(fmaxf(fmaf(nb.z, ix, bnx), fmaf(nb.w, iy, bny)), fmaf(nc.x, iz, bnz));
+            const float f1 = fminf(fminf(fmaf(nc.y, ix, bfx), fmaf(nc.z, iy, bfy)), fmaf(nc.w, iz, bfz));
+            const bool h0 = !(n0 > f0) && !(f0 < 0.f) && !(n0 > rec.t);   // written so that a NaN bound passes
+            const bool h1 = !(n1 > f1) && !(f1 < 0.f) && !(n1 > rec.t);
+            if (h0 && h1) {
+                const bool swap = n1 < n0;
+                node = swap ? ch.y : ch.x;
+                stack[sp++] = swap ? ch.x : ch.y;
+                continue;
+            }
+            if (h0 || h1) { node = h0 ? ch.x : ch.y; continue; }
+        } else {
+            const int l = ~node;
+            hit_ordered(__ldg(&scene.leafShape[l]), (int)__ldg(&scene.leafDevice[l]), __ldg(&scene.leafOrig[l]), ray, a, rec);
+            n.tests++;
+        }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+}
+#elif LBVH_WHILE
     // while-while: a warp first walks inner nodes until every lane holds a leaf (or is done), then tests the leaves together
     constexpr int kDone = (int)0x80000000;   // = ~0x7fffffff, never a leaf
     stack[0] = kDone;

@@ -31,6 +31,9 @@ struct BvhNode {
     int pad0, pad1;
 };
 
+// The traversal reads octant copies of the node array: copy o (bit a set = direction component a < 0) holds, in BvhNode's
+// layout, each child's NEAR planes where BvhNode has the minimum and its FAR planes where BvhNode has the maximum, so a
+// ray picks its planes once (one base pointer) instead of with 12 selects per visit.
 struct BvhBuildArgs {
     const float4* shape;        // device-order (cx, cy, cz, r); the first `count` entries go into the tree
     const uint32_t* origIndex;  // device index -> index in the caller's array
@@ -41,6 +44,7 @@ struct BvhBuildArgs {
     uint32_t* leafOrig;            // [count] sorted original index
     uint32_t* leafDevice;          // [count] sorted device index (surf / kind lookup)
     BvhNode* nodes;                // [count-1]
+    BvhNode* octNodes;             // [8][count-1], see above
     int* parent;                   // [2*count-1]: internal nodes 0..count-2, then leaves
     float* bounds;                 // [2*count-1][6] min.xyz max.xyz of every node / leaf
     unsigned int* arrivals;        // [count-1]
@@ -132,6 +136,19 @@ __global__ void lbvh_refit_kernel(BvhBuildArgs g) {
         nd.a = make_float4(v0[0], v0[1], v0[2], v0[3]);
         nd.b = make_float4(v0[4], v0[5], v1[0], v1[1]);
         nd.c = make_float4(v1[2], v1[3], v1[4], v1[5]);
+        for (int o = 0; o < 8; o++) {
+            float w0[6], w1[6];
+            for (int a = 0; a < 3; a++) {
+                const bool neg = (o >> a) & 1;
+                w0[a] = neg ? v0[3 + a] : v0[a]; w0[3 + a] = neg ? v0[a] : v0[3 + a];
+                w1[a] = neg ? v1[3 + a] : v1[a]; w1[3 + a] = neg ? v1[a] : v1[3 + a];
+            }
+            BvhNode& on = g.octNodes[(size_t)o * (size_t)(n - 1) + node];
+            on.a = make_float4(w0[0], w0[1], w0[2], w0[3]);
+            on.b = make_float4(w0[4], w0[5], w1[0], w1[1]);
+            on.c = make_float4(w1[2], w1[3], w1[4], w1[5]);
+            on.child0 = nd.child0; on.child1 = nd.child1; on.pad0 = 0; on.pad1 = 0;
+        }
         float* bb = g.bounds + 6 * (size_t)node;
         for (int k = 0; k < 3; k++) { __stcg(bb + k, fminf(v0[k], v1[k])); __stcg(bb + 3 + k, fmaxf(v0[3 + k], v1[3 + k])); }
         node = g.parent[node];

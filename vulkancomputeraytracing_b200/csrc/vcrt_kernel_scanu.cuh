@@ -166,30 +166,36 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
             //      thread's rays and one compare against the sphere's scalar; survivors set a bit, and after every block of
             //      32 spheres the set bits are appended to the thread's candidate list.
             //      q' = (c.dh + e)^2 - (c.A + B)  >=  |c|^2 - R2   <=>  the sphere may be hit
-#pragma unroll 1
-            for (int base = 0; base < scanPad; base += 32) {
-                uint32_t mask = 0u;
-                const int lim = min(32, scanPad - base);   // scanPad is a multiple of 16
-#pragma unroll 1
-                for (int kk = 0; kk < lim; kk += UNROLL) {
-                    uint32_t mEven = 0u, mOdd = 0u;   // two accumulators: half the dependent-OR chain
+            // U spheres starting at `at`: bit u of the result = sphere at + u may be hit by one of the thread's rays
+            auto scan_block = [&]<int U>(int at) -> uint32_t {
+                uint32_t mEven = 0u, mOdd = 0u;   // two accumulators: half the dependent-OR chain
 #pragma unroll
-                    for (int u = 0; u < UNROLL; u++) {
-                        const float4 s = cSceneHot[base + kk + u];
-                        const u64 cx = pack2(s.x, s.x), cy = pack2(s.y, s.y), cz = pack2(s.z, s.z);
-                        float qmax = -kPosInf;
+                for (int u = 0; u < U; u++) {
+                    const float4 s = cSceneHot[at + u];
+                    const u64 cx = pack2(s.x, s.x), cy = pack2(s.y, s.y), cz = pack2(s.z, s.z);
+                    float qmax = -kPosInf;
 #pragma unroll
-                        for (int p = 0; p < PAIRS; p++) {
-                            u64 t = ffma2(cz, dz[p], ee[p]); t = ffma2(cy, dy[p], t); t = ffma2(cx, dx[p], t);
-                            u64 w = ffma2(cz, az[p], nb[p]); w = ffma2(cy, ay[p], w); w = ffma2(cx, ax[p], w);
-                            const u64 q = ffma2(t, t, w);
-                            float q0, q1; unpack2(q, q0, q1);
-                            qmax = fmaxf(qmax, fmaxf(q0, q1));
-                        }
-                        flag_if_ge(u & 1 ? mOdd : mEven, qmax, s.w, 1u << u);
+                    for (int p = 0; p < PAIRS; p++) {
+                        u64 t = ffma2(cz, dz[p], ee[p]); t = ffma2(cy, dy[p], t); t = ffma2(cx, dx[p], t);
+                        u64 w = ffma2(cz, az[p], nb[p]); w = ffma2(cy, ay[p], w); w = ffma2(cx, ax[p], w);
+                        const u64 q = ffma2(t, t, w);
+                        float q0, q1; unpack2(q, q0, q1);
+                        qmax = fmaxf(qmax, fmaxf(q0, q1));
                     }
-                    mask |= (mEven | mOdd) << kk;
+                    flag_if_ge(u & 1 ? mOdd : mEven, qmax, s.w, 1u << u);
                 }
+                return mEven | mOdd;
+            };
+            const int scanLim = (scanCount + 3) & ~3;   // the table is padded (never-passing entries) to a multiple of 16
+#pragma unroll 1
+            for (int base = 0; base < scanLim; base += 32) {
+                uint32_t mask = 0u;
+                const int lim = min(32, scanLim - base);
+                int kk = 0;
+#pragma unroll 1
+                for (; kk + UNROLL <= lim; kk += UNROLL) mask |= scan_block.template operator()<UNROLL>(base + kk) << kk;
+#pragma unroll 1
+                for (; kk < lim; kk += 4) mask |= scan_block.template operator()<4>(base + kk) << kk;   // the tail, 4 at a time
                 while (mask) {
                     const int k = __ffs(mask) - 1;
                     mask &= mask - 1u;

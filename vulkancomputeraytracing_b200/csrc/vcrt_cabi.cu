@@ -611,7 +611,7 @@ static bool scanUFits(int threads, int pairs, int lcap) {
 }
 
 static const size_t kSmemBudget = 227 * 1024;
-static const uint32_t kBruteForceLimit = 48;   // spheres; above this VCRT_TRAVERSAL_AUTO takes the LBVH
+static const uint32_t kBruteForceLimit = 6;   // spheres; above this VCRT_TRAVERSAL_AUTO takes the LBVH (measured faster from 8 spheres up)
 static bool scanFits(int threads, int pairs, int cap) {
     size_t state = (size_t)SF_COUNT * 2 * pairs * threads * 4, lists = (size_t)(cap + 2) * 2 * pairs * threads * 2;
     return 16 + (size_t)cudaComputeSceneHeader.bytes + state + lists <= kSmemBudget && cudaComputeSceneHeader.scanPad < 65536u;
@@ -625,8 +625,8 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     if (!cudaComputeSceneReady) return fail(VCRT_ERROR_NOT_READY, "cudaRender before cudaUploadScene%s", "");
 
     uint32_t traversal = p->traversal;
-    // AUTO = the fastest: the LBVH beats the brute-force scan from a few dozen spheres on (measured 2.0x at 485 spheres,
-    // DESIGN.md section 6); below that the tree has nothing to prune and the scan's regular inner loop wins
+    // AUTO = the fastest: the LBVH beats the brute-force scan from 8 spheres on (1.05x at 8, 1.5x at 100, 2.9x at 485 spheres,
+    // DESIGN.md section 6); only a handful of spheres leaves the tree nothing to prune
     if (traversal == VCRT_TRAVERSAL_AUTO)
         traversal = (cudaComputeSceneHeader.count <= kBruteForceLimit && (scanUFits(1024, 1, 30) || scanFits(256, 2, 12))) ? VCRT_TRAVERSAL_BRUTE : VCRT_TRAVERSAL_LBVH;
     if (traversal == VCRT_TRAVERSAL_BRUTE && !scanFits(256, 2, 12) && !scanUFits(512, 2, 30))

@@ -328,3 +328,16 @@ def test_acceptance_path_lengths_and_materials_vs_the_references_own_rng(oracle,
     assert np.all(np.abs(got / want - 1) < 2e-2), (got, want)
     hits, rhits = np.array(st.hitsByMaterial, float), np.array(ref["hits"], float)
     assert np.all(np.abs(hits[1:] / rhits[1:] - 1) < 2e-2) and hits[0] == rhits[0] == 0
+
+
+def test_more_than_2_to_the_32_pixel_samples_in_one_call(gpu_scene):
+    # 3840x2160x520 spp = 4.31e9 pixel-samples: the 32-bit work-item numbering has to group samples (it used to wrap silently)
+    w, h, spp = 3840, 2160, 520
+    img, st = host.render(w, h, spp, traversal=LBVH)
+    assert st.samples == w * h * spp > 2 ** 32
+    assert abs(st.rays / st.samples / 2.2975 - 1) < 5e-3
+    with open(os.path.join(GOLDEN, "ref_kat.json")) as f:
+        want = json.load(f)["render_400x225_s16"]["mean_rgb"]          # same framing at any 16:9 size (bug B1)
+    mean = img[..., :3].reshape(-1, 3).astype(np.float64).mean(0)
+    assert np.all(np.abs(mean / np.array(want) - 1) < 5e-3)
+    host.render(16, 16, 1, traversal=LBVH, download=False)              # give the 4K buffers back to smaller ones

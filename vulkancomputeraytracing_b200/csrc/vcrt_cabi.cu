@@ -647,7 +647,28 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         if (chunks < 1u) chunks = 1u;
     }
     if (traversal == VCRT_TRAVERSAL_LBVH) { rc = ensureBvh(); if (rc) return rc; }
-    const uint32_t samplesPerItem = p->reserved[0] ? p->reserved[0] : 1u;   // measured: 1 is fastest (keeps the lanes of a warp on neighbouring pixels)
+    // Work items.  Fixed-point mode: 1 sample per item is fastest (measured; it keeps the lanes of a warp on neighbouring
+    // pixels); more only where the 32-bit item numbering needs it (4K x 520 spp on one GPU is already 2^32 pixel-samples).
+    // Strict modes: one item per pixel and chunk.
+    ItemPlan plan; memset(&plan, 0, sizeof plan);
+    {
+        const uint64_t tiles = (uint64_t)((p->width + 7u) / 8u) * ((p->height + 3u) / 4u);
+        if (tiles * 32u >= (1ull << 31)) return fail(VCRT_ERROR_INVALID_ARGUMENT, "image too large%s", "");
+        plan.tilesX = (p->width + 7u) / 8u; plan.pixelsPadded = (uint32_t)(tiles * 32u);
+        uint32_t perRun = fixedMode ? (p->reserved[0] ? p->reserved[0] : 1u) : (p->samplesPerPixel + chunks - 1u) / chunks;
+        const uint64_t padded = plan.pixelsPadded > kBandPixels ? plan.pixelsPadded : kBandPixels;
+        const uint64_t need = (padded * p->samplesPerPixel + (1ull << 31) - 1) >> 31;   // runs x padded pixels < 2^31
+        if (fixedMode && need > perRun) perRun = (uint32_t)need;
+        if (perRun < 1u) perRun = 1u;
+        plan.sppPerRun = perRun; plan.runsPerPixel = (p->samplesPerPixel + perRun - 1u) / perRun;
+        if ((uint64_t)plan.pixelsPadded * plan.runsPerPixel >= (1ull << 31)) return fail(VCRT_ERROR_INVALID_ARGUMENT, "too many work items: lower sampleChunks%s", "");
+        plan.totalItems = plan.pixelsPadded * plan.runsPerPixel;
+        const uint32_t fullBands = plan.pixelsPadded >> VCRT_BAND_SHIFT;
+        plan.fullBandRuns = fullBands * plan.runsPerPixel;
+        plan.lastBandFirst = fullBands << VCRT_BAND_SHIFT; plan.lastBandPixels = plan.pixelsPadded - plan.lastBandFirst;
+        plan.invRuns = plan.runsPerPixel ? 1.0f / (float)plan.runsPerPixel : 0.f;
+        plan.invLastBand = plan.lastBandPixels ? 1.0f / (float)plan.lastBandPixels : 0.f;
+    }
     rc = ensureImageBuffers(p->width, p->height, chunks); if (rc) return rc;
     const bool keep = (p->flags & VCRT_FLAG_ACCUMULATE) && cudaComputeAccumulatedSamples > 0;
     if (keep && fixedMode != cudaComputeAccumulatedIsFixed)
@@ -661,7 +682,7 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     args.width = p->width; args.height = p->height; args.spp = p->samplesPerPixel; args.sampleOffset = p->sampleOffset;
     args.maxDepth = p->maxDepth; args.seedLo = (uint32_t)p->seed; args.seedHi = (uint32_t)(p->seed >> 32);
     args.chunks = chunks; args.flags = p->flags; args.sums = cudaComputeSumPlanes;
-    args.fixedSums = cudaComputeFixedSums; args.samplesPerItem = samplesPerItem;
+    args.fixedSums = cudaComputeFixedSums; args.plan = plan;
     args.counters = cudaComputeCounters; args.workCounter = cudaComputeWorkCounter;
 
     uint32_t launches = 0;

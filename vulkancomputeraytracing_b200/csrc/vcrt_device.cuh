@@ -90,6 +90,28 @@ struct DeviceScene {
 // Camera frame of shader.comp:18-39, computed once on the host in the same binary32 order.
 struct Frame { V3 center, pixel00, du, dv; };
 
+// How a launch's work items (one pixel, one run of consecutive samples) are numbered; filled by the host (make_item_plan
+// in vcrt_cabi.cu) so that the kernels read it from the constant bank instead of keeping it in registers.
+// Items are numbered band by band: all runs of the first kBandPixels pixels, then all runs of the next band, ...  The
+// paths in flight (3e5 per GPU) then touch a few MB of the accumulation buffer at a time, which stays in L2; numbering
+// sample-major instead sweeps the whole buffer once per sample and made L2 write every RED through to DRAM (29.7 GB per
+// C2 launch against 33 MB of image, profiles/traffic.json).
+#ifndef VCRT_BAND_SHIFT
+#define VCRT_BAND_SHIFT 18
+#endif
+constexpr uint32_t kBandPixels = 1u << VCRT_BAND_SHIFT;   // padded pixels (whole 8x4 tiles); 8 MB of sums per band
+struct ItemPlan {
+    uint32_t tilesX;          // 8x4-pixel tiles per row; pixels are walked tile by tile so that a warp starts on one tile
+    uint32_t pixelsPadded;    // tiles * 32
+    uint32_t sppPerRun;       // samples per item
+    uint32_t runsPerPixel;    // ceil(spp / sppPerRun)
+    uint32_t totalItems;      // pixelsPadded * runsPerPixel, < 2^31
+    uint32_t fullBandRuns;    // (pixelsPadded >> VCRT_BAND_SHIFT) * runsPerPixel
+    uint32_t lastBandFirst;   // first padded pixel of the last, short band
+    uint32_t lastBandPixels;  // its size (may be 0)
+    float invRuns, invLastBand;   // reciprocals for the float-estimate divisions
+};
+
 struct RenderArgs {
     Frame frame;
     uint32_t width, height;
@@ -101,7 +123,7 @@ struct RenderArgs {
     uint32_t flags;
     float4* sums;           // float modes: [chunks][height*width] (x,y,z = sums, w unused)
     long long* fixedSums;   // fixed-point mode: [height*width][4] signed 32.32 sums (r, g, b, unused)
-    uint32_t samplesPerItem;  // fixed-point mode: samples per work item
+    ItemPlan plan;
     uint32_t semantics;       // 0 = the reference shader as it is, 1 = BOOK (vcrt_shade.cuh)
     unsigned long long* counters;  // see Counter enum
     unsigned int* workCounter;     // dynamic item dispenser
@@ -109,6 +131,26 @@ struct RenderArgs {
 
 enum Counter { CTR_RAYS = 0, CTR_EXHAUSTED, CTR_BAD_MATERIAL, CTR_CANDIDATES, CTR_OVERFLOWS, CTR_TESTS, CTR_NODES,
                CTR_HITS0, CTR_HITS1, CTR_HITS2, CTR_HITS3, CTR_PATH0, CTR_COUNT = CTR_PATH0 + 8 };
+
+// x / d given inv ~ 1 / d, for quotients below 2^22 and d below 2^24: float estimate (within 1), one correction step
+__device__ __forceinline__ uint32_t udiv_small(uint32_t x, uint32_t d, float inv, uint32_t& rem) {
+    uint32_t q = __float2uint_rz(__uint2float_rz(x) * inv);
+    int r = (int)(x - q * d);
+    if (r < 0) { q--; r += (int)d; } else if (r >= (int)d) { q++; r -= (int)d; }
+    rem = (uint32_t)r;
+    return q;
+}
+// item id -> (run index within the pixel, padded pixel index)
+__device__ __forceinline__ void item_to_run(const ItemPlan& plan, uint32_t id, uint32_t& chunk, uint32_t& pid) {
+    const uint32_t bandRun = id >> VCRT_BAND_SHIFT;            // = band * runsPerPixel + chunk while the band is a full one
+    if (bandRun < plan.fullBandRuns) {
+        const uint32_t band = udiv_small(bandRun, plan.runsPerPixel, plan.invRuns, chunk);
+        pid = (band << VCRT_BAND_SHIFT) | (id & (kBandPixels - 1u));
+    } else {                                                   // the last, short band
+        chunk = udiv_small(id - plan.lastBandFirst * plan.runsPerPixel, plan.lastBandPixels, plan.invLastBand, pid);
+        pid += plan.lastBandFirst;
+    }
+}
 
 constexpr uint32_t kFlagCountStats = 1u << 3;   // VCRT_FLAG_COUNT_STATS of include/vcrt.h
 

@@ -73,11 +73,9 @@ VCRT_DEV void hit_ordered(float4 shape, int device, uint32_t orig, const Ray& r,
 template <bool FIXED, bool STATS>
 __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_kernel(BvhScene scene, RenderArgs args) {
     const uint32_t pixels = args.width * args.height;
-    const uint32_t sppPerChunk = FIXED ? args.samplesPerItem : (args.spp + args.chunks - 1u) / args.chunks;
-    const uint32_t runsPerPixel = (args.spp + sppPerChunk - 1u) / sppPerChunk;
+    const uint32_t sppPerChunk = args.plan.sppPerRun;   // host-made plan (vcrt_device.cuh)
     // items walk the image in 8x4 pixel tiles so a warp starts on one tile
-    const uint32_t tilesX = (args.width + 7u) / 8u, tilesY = (args.height + 3u) / 4u, pixelsPadded = tilesX * tilesY * 32u;
-    const uint32_t totalItems = pixelsPadded * runsPerPixel;
+    const uint32_t tilesX = args.plan.tilesX, totalItems = args.plan.totalItems;
     uint32_t nRays = 0, nNodes = 0, nTests = 0, nExhausted = 0, nBad = 0;   // per thread; widened when summed
     int stack[64];
 
@@ -85,7 +83,8 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_kernel(BvhScene 
     const uint32_t firstDynamic = gridDim.x * blockDim.x;
     for (;; item = firstDynamic + atomicAdd(args.workCounter, 1u)) {
         if (item >= totalItems) break;
-        const uint32_t chunk = item / pixelsPadded, pid = item - chunk * pixelsPadded;
+        uint32_t chunk, pid;
+        item_to_run(args.plan, item, chunk, pid);
         const uint32_t tile = pid >> 5, within = pid & 31u, ty = tile / tilesX, tx = tile - ty * tilesX;
         const uint32_t px = tx * 8u + (within & 7u), py = ty * 4u + (within >> 3);
         if (px >= args.width || py >= args.height) continue;
@@ -365,10 +364,8 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
 template <bool FIXED, bool STATS>
 __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhScene scene, RenderArgs args) {
     const uint32_t pixels = args.width * args.height;
-    const uint32_t sppPerChunk = FIXED ? args.samplesPerItem : (args.spp + args.chunks - 1u) / args.chunks;
-    const uint32_t runsPerPixel = (args.spp + sppPerChunk - 1u) / sppPerChunk;
-    const uint32_t tilesX = (args.width + 7u) / 8u, tilesY = (args.height + 3u) / 4u, pixelsPadded = tilesX * tilesY * 32u;
-    const uint32_t totalItems = pixelsPadded * runsPerPixel;
+    const uint32_t sppPerChunk = args.plan.sppPerRun;   // host-made plan (vcrt_device.cuh)
+    const uint32_t tilesX = args.plan.tilesX, totalItems = args.plan.totalItems;
     LbvhCounts n = {0u, 0u, 0u, 0u, 0u};
     int stack[65];
 
@@ -395,8 +392,8 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhS
                 if (!firstItem) item = firstDynamic + atomicAdd(args.workCounter, 1u);
                 firstItem = false;
                 if (item >= totalItems) break;
-                chunk = item / pixelsPadded;
-                const uint32_t pid = item - chunk * pixelsPadded;
+                uint32_t pid;
+                item_to_run(args.plan, item, chunk, pid);
                 const uint32_t tile = pid >> 5, within = pid & 31u, ty = tile / tilesX, tx = tile - ty * tilesX;
                 px = tx * 8u + (within & 7u); py = ty * 4u + (within >> 3);
                 if (px >= args.width || py >= args.height) continue;

@@ -111,10 +111,9 @@ struct ScanConfig {
 constexpr uint32_t kIdle = 0xffffffffu;
 
 // Item id -> pixel.  Items walk the image in 8x4 tiles so the 32 lanes of a warp start on one tile.
-struct ItemMap { uint32_t tilesX, tilesY, pixelsPadded; };
-VCRT_DEV bool item_to_pixel(const ItemMap& map, uint32_t width, uint32_t height, uint32_t id, uint32_t& px, uint32_t& py) {
+VCRT_DEV bool item_to_pixel(uint32_t tilesX, uint32_t width, uint32_t height, uint32_t id, uint32_t& px, uint32_t& py) {
     uint32_t tile = id >> 5, within = id & 31u;
-    uint32_t ty = tile / map.tilesX, tx = tile - ty * map.tilesX;
+    uint32_t ty = tile / tilesX, tx = tile - ty * tilesX;
     px = tx * 8u + (within & 7u);
     py = ty * 4u + (within >> 3);
     return px < width && py < height;
@@ -151,15 +150,10 @@ __global__ void __launch_bounds__(THREADS, 1) render_scan_kernel(const unsigned 
     uint32_t* sCount = reinterpret_cast<uint32_t*>(sList + CAP * R * THREADS);
 #define CNT(r) sCount[(r) * THREADS + tid]
 
-    ItemMap map;
-    map.tilesX = (args.width + 7u) / 8u; map.tilesY = (args.height + 3u) / 4u;
-    map.pixelsPadded = map.tilesX * map.tilesY * 32u;
     // Work item = (pixel, run of consecutive samples).  Float modes: args.chunks runs per pixel, each summed in
-    // sample order into its own plane.  Fixed-point mode: runs of args.samplesPerItem, every sample added to the
+    // sample order into its own plane.  Fixed-point mode: short runs (1 sample unless the item count needs more), every sample added to the
     // pixel's 32.32 integer sums with a RED (order-independent, so any schedule gives the same bits).
-    const uint32_t sppPerChunk = FIXED ? args.samplesPerItem : (args.spp + args.chunks - 1u) / args.chunks;
-    const uint32_t runsPerPixel = (args.spp + sppPerChunk - 1u) / sppPerChunk;
-    const uint32_t totalItems = map.pixelsPadded * runsPerPixel;
+    const uint32_t sppPerChunk = args.plan.sppPerRun, totalItems = args.plan.totalItems;   // host-made plan (vcrt_device.cuh)
     const uint32_t planeStride = args.width * args.height;
 
     unsigned long long nRays = 0;
@@ -173,8 +167,9 @@ __global__ void __launch_bounds__(THREADS, 1) render_scan_kernel(const unsigned 
             if (!have) id = atomicAdd(args.workCounter, 1u);
             have = false;
             if (id >= totalItems) { ST(SF_PIXEL, r) = kIdle; return false; }
-            uint32_t chunk = id / map.pixelsPadded, pid = id - chunk * map.pixelsPadded, px, py;
-            if (!item_to_pixel(map, args.width, args.height, pid, px, py)) continue;
+            uint32_t chunk, pid, px, py;
+            item_to_run(args.plan, id, chunk, pid);
+            if (!item_to_pixel(args.plan.tilesX, args.width, args.height, pid, px, py)) continue;
             uint32_t s0 = chunk * sppPerChunk, s1 = min(args.spp, s0 + sppPerChunk);
             if (s0 >= s1) continue;
             ST(SF_PIXEL, r) = py * args.width + px;

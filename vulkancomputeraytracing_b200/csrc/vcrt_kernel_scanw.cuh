@@ -69,12 +69,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanw_kernel(const unsigned
 #define WSF(field, r, t) __uint_as_float(WS(field, r, t))
 #define TLIST(e) sList[(e) * THREADS + tid]
 
-    ItemMap map;
-    map.tilesX = (args.width + 7u) / 8u; map.tilesY = (args.height + 3u) / 4u;
-    map.pixelsPadded = map.tilesX * map.tilesY * 32u;
-    const uint32_t sppPerChunk = FIXED ? args.samplesPerItem : (args.spp + args.chunks - 1u) / args.chunks;
-    const uint32_t runsPerPixel = (args.spp + sppPerChunk - 1u) / sppPerChunk;
-    const uint32_t totalItems = map.pixelsPadded * runsPerPixel;
+    const uint32_t sppPerChunk = args.plan.sppPerRun, totalItems = args.plan.totalItems;   // host-made plan, constant bank
     const uint32_t planeStride = args.width * args.height;
 
     unsigned long long nRays = 0;
@@ -87,8 +82,9 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanw_kernel(const unsigned
             if (!have) id = atomicAdd(args.workCounter, 1u);
             have = false;
             if (id >= totalItems) { WS(WF_PIXEL, r, t) = kIdle; return false; }
-            uint32_t chunk = id / map.pixelsPadded, pid = id - chunk * map.pixelsPadded, px, py;
-            if (!item_to_pixel(map, args.width, args.height, pid, px, py)) continue;
+            uint32_t chunk, pid, px, py;
+            item_to_run(args.plan, id, chunk, pid);
+            if (!item_to_pixel(args.plan.tilesX, args.width, args.height, pid, px, py)) continue;
             uint32_t s0 = chunk * sppPerChunk, s1 = min(args.spp, s0 + sppPerChunk);
             if (s0 >= s1) continue;
             WS(WF_PIXEL, r, t) = py * args.width + px;

@@ -341,3 +341,20 @@ def test_more_than_2_to_the_32_pixel_samples_in_one_call(gpu_scene):
     mean = img[..., :3].reshape(-1, 3).astype(np.float64).mean(0)
     assert np.all(np.abs(mean / np.array(want) - 1) < 5e-3)
     host.render(16, 16, 1, traversal=LBVH, download=False)              # give the 4K buffers back to smaller ones
+
+
+def test_item_numbering_corner_cases(oracle, gpu_scene):
+    # one tile and very many samples (runs per pixel are capped), an image of exactly one band and one pixel more, strict chunks
+    img, st = host.render(8, 4, 5_000_000, depth=2, traversal=BRUTE)
+    assert st.samples == 32 * 5_000_000 and 0 < st.rays <= 2 * st.samples and np.isfinite(img).all()
+    for w, h in ((512, 512), (513, 512), (1024, 257)):                  # 2^18 padded pixels, and just above
+        cpu, cst = oracle.render(gpu_scene, w, h, 1, depth=3)
+        for trav in (BRUTE, LBVH):
+            gpu, sg = host.render(w, h, 1, depth=3, traversal=trav, sample_chunks=1)
+            assert_same(gpu, sg, cpu, cst)
+            fixed, sf = host.render(w, h, 1, depth=3, traversal=trav)
+            assert sf.rays == cst["rays"] and np.abs(fixed - cpu).max() <= 2.0 ** -22
+    cpu, cst = oracle.render(gpu_scene, 96, 54, 7)
+    for chunks in (2, 3, 7):                                              # float sums per chunk, chunks combined in order
+        gpu, sg = host.render(96, 54, 7, traversal=LBVH, sample_chunks=chunks)
+        assert sg.rays == cst["rays"] and np.abs(gpu - cpu).max() <= 2.0 ** -20

@@ -656,18 +656,20 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         if (tiles * 32u >= (1ull << 31)) return fail(VCRT_ERROR_INVALID_ARGUMENT, "image too large%s", "");
         plan.tilesX = (p->width + 7u) / 8u; plan.pixelsPadded = (uint32_t)(tiles * 32u);
         uint32_t perRun = fixedMode ? (p->reserved[0] ? p->reserved[0] : 1u) : (p->samplesPerPixel + chunks - 1u) / chunks;
-        const uint64_t padded = plan.pixelsPadded > kBandPixels ? plan.pixelsPadded : kBandPixels;
-        const uint64_t need = (padded * p->samplesPerPixel + (1ull << 31) - 1) >> 31;   // runs x padded pixels < 2^31
+        const uint64_t kMaxItems = (1ull << 32) - (1ull << 24);
+        const uint64_t need = ((uint64_t)plan.pixelsPadded * p->samplesPerPixel + kMaxItems - 1) / kMaxItems;
         if (fixedMode && need > perRun) perRun = (uint32_t)need;
+        if (fixedMode && p->samplesPerPixel / perRun >= (1u << 21)) perRun = p->samplesPerPixel >> 21;   // keeps runsPerPixel < 2^22
         if (perRun < 1u) perRun = 1u;
         plan.sppPerRun = perRun; plan.runsPerPixel = (p->samplesPerPixel + perRun - 1u) / perRun;
-        if ((uint64_t)plan.pixelsPadded * plan.runsPerPixel >= (1ull << 31)) return fail(VCRT_ERROR_INVALID_ARGUMENT, "too many work items: lower sampleChunks%s", "");
+        if ((uint64_t)plan.pixelsPadded * plan.runsPerPixel > kMaxItems || plan.runsPerPixel >= (1u << 22))
+            return fail(VCRT_ERROR_INVALID_ARGUMENT, "too many work items: lower sampleChunks / samplesPerPixel per call%s", "");
         plan.totalItems = plan.pixelsPadded * plan.runsPerPixel;
         const uint32_t fullBands = plan.pixelsPadded >> VCRT_BAND_SHIFT;
         plan.fullBandRuns = fullBands * plan.runsPerPixel;
         plan.lastBandFirst = fullBands << VCRT_BAND_SHIFT; plan.lastBandPixels = plan.pixelsPadded - plan.lastBandFirst;
-        plan.invRuns = plan.runsPerPixel ? 1.0f / (float)plan.runsPerPixel : 0.f;
-        plan.invLastBand = plan.lastBandPixels ? 1.0f / (float)plan.lastBandPixels : 0.f;
+        plan.invRuns = plan.runsPerPixel ? nextafterf(1.0f / (float)plan.runsPerPixel, 0.f) : 0.f;
+        plan.invLastBand = plan.lastBandPixels ? nextafterf(1.0f / (float)plan.lastBandPixels, 0.f) : 0.f;
     }
     rc = ensureImageBuffers(p->width, p->height, chunks); if (rc) return rc;
     const bool keep = (p->flags & VCRT_FLAG_ACCUMULATE) && cudaComputeAccumulatedSamples > 0;

@@ -105,11 +105,11 @@ struct ItemPlan {
     uint32_t pixelsPadded;    // tiles * 32
     uint32_t sppPerRun;       // samples per item
     uint32_t runsPerPixel;    // ceil(spp / sppPerRun)
-    uint32_t totalItems;      // pixelsPadded * runsPerPixel, < 2^31
+    uint32_t totalItems;      // pixelsPadded * runsPerPixel, <= 2^32 - 2^24 (the dispenser counts a little past it)
     uint32_t fullBandRuns;    // (pixelsPadded >> VCRT_BAND_SHIFT) * runsPerPixel
     uint32_t lastBandFirst;   // first padded pixel of the last, short band
     uint32_t lastBandPixels;  // its size (may be 0)
-    float invRuns, invLastBand;   // reciprocals for the float-estimate divisions
+    float invRuns, invLastBand;   // reciprocals, rounded down, for the float-estimate divisions
 };
 
 struct RenderArgs {
@@ -132,12 +132,14 @@ struct RenderArgs {
 enum Counter { CTR_RAYS = 0, CTR_EXHAUSTED, CTR_BAD_MATERIAL, CTR_CANDIDATES, CTR_OVERFLOWS, CTR_TESTS, CTR_NODES,
                CTR_HITS0, CTR_HITS1, CTR_HITS2, CTR_HITS3, CTR_PATH0, CTR_COUNT = CTR_PATH0 + 8 };
 
-// x / d given inv ~ 1 / d, for quotients below 2^22 and d below 2^24: float estimate (within 1), one correction step
+// x / d given inv <= 1 / d (rounded down), for quotients below 2^22 and d below 2^24: the float estimate never exceeds the
+// quotient and is at most 2 short of it
 __device__ __forceinline__ uint32_t udiv_small(uint32_t x, uint32_t d, float inv, uint32_t& rem) {
-    uint32_t q = __float2uint_rz(__uint2float_rz(x) * inv);
-    int r = (int)(x - q * d);
-    if (r < 0) { q--; r += (int)d; } else if (r >= (int)d) { q++; r -= (int)d; }
-    rem = (uint32_t)r;
+    uint32_t q = __float2uint_rz(__fmul_rz(__uint2float_rz(x), inv));
+    uint32_t r = x - q * d;
+    if (r >= d) { q++; r -= d; }
+    if (r >= d) { q++; r -= d; }
+    rem = r;
     return q;
 }
 // item id -> (run index within the pixel, padded pixel index)

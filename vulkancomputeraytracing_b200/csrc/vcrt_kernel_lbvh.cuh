@@ -389,7 +389,7 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhS
                     if (!FIXED) args.sums[(size_t)chunk * pixels + pixel] = make_float4(sum.x, sum.y, sum.z, 0.f);
                     haveRun = false;
                 }
-                if (!firstItem) item = firstDynamic + atomicAdd(args.workCounter, 1u);
+                if (!firstItem) item = firstDynamic + atomicAdd(args.workCounter, 1u);   // (an explicit warp-aggregated claim is 1.3 % slower)
                 firstItem = false;
                 if (item >= totalItems) break;
                 uint32_t pid;

@@ -358,3 +358,32 @@ def test_item_numbering_corner_cases(oracle, gpu_scene):
     for chunks in (2, 3, 7):                                              # float sums per chunk, chunks combined in order
         gpu, sg = host.render(96, 54, 7, traversal=LBVH, sample_chunks=chunks)
         assert sg.rays == cst["rays"] and np.abs(gpu - cpu).max() <= 2.0 ** -20
+
+
+@pytest.mark.parametrize("case", ["zero_and_negative_radius", "tiny_and_huge", "nan_and_inf_spheres", "degenerate_camera", "coincident_centres"])
+def test_pathological_inputs_follow_the_reference_arithmetic(oracle, vcrt, case):
+    # inputs the reference never guards against: whatever binary32 arithmetic makes of them, all traversals make the same
+    rng = np.random.default_rng(zlib.crc32(case.encode()))
+    scene = random_scene(rng, 40)
+    cam = cabi.VcrtCamera((ctypes.c_float * 3)(0, 1, 14), (ctypes.c_float * 3)(0, 0, 0), (ctypes.c_float * 3)(0, 1, 0), 50.0)
+    if case == "zero_and_negative_radius":
+        scene[0:5, 3] = 0.0; scene[5:10, 3] = -scene[5:10, 3]          # r = 0 never hits; r < 0 hits with an inward "outward" normal
+    elif case == "tiny_and_huge":
+        scene[0:4, 3] = 1e-20; scene[4:6, 0:3] *= 1e17; scene[6, 3] = 3e18; scene[7, 0:3] = [1e-30, 1e-30, 1e-30]
+    elif case == "nan_and_inf_spheres":
+        scene[0, 0] = np.nan; scene[1, 3] = np.inf; scene[2, 1] = -np.inf; scene[3, 3] = np.nan; scene[4, 4:7] = np.nan
+    elif case == "degenerate_camera":
+        cam = cabi.VcrtCamera((ctypes.c_float * 3)(1, 2, 3), (ctypes.c_float * 3)(1, 2, 3), (ctypes.c_float * 3)(0, 1, 0), 50.0)   # lookfrom == lookat
+    else:
+        scene[0:20, 0:3] = scene[0, 0:3]; scene[0:20, 3] = np.linspace(0.5, 1.5, 20)   # 20 concentric spheres of three materials
+    host.upload_scene(scene, cam)
+    try:
+        cpu, cst = oracle.render(scene, 64, 48, 2, depth=12, camera=host.camera_array(cam))
+        for traversal in (SIMPLE, BRUTE, LBVH):
+            gpu, st = host.render(64, 48, 2, depth=12, traversal=traversal, sample_chunks=1)
+            assert st.rays == cst["rays"] and st.depthExhausted == cst["exhausted"], (traversal, st.rays, cst["rays"])
+            assert np.array_equal(gpu, cpu, equal_nan=True), traversal
+            again, _ = host.render(64, 48, 2, depth=12, traversal=traversal)          # fixed-point accumulation must not trap on NaN either
+            assert again.shape == gpu.shape
+    finally:
+        host.destroy()

@@ -38,6 +38,7 @@ static unsigned char* cudaComputeSceneBlob = nullptr;   // device copy of the So
 static SceneBlob cudaComputeSceneHeader;
 static bool cudaComputeSceneReady = false;
 static bool cudaComputeSceneInConstant = false;   // the filter table of the uniform-datapath scan is loaded
+static bool cudaComputeSceneNonFinite = false;    // a centre or radius is NaN / inf: only the in-order scan reproduces the reference
 struct SceneExtent { float centreMin[3], centreMax[3], radiusMin, radiusMax; };
 static SceneExtent cudaComputeSceneExtent;
 // LBVH over the scan spheres (device indices [0, scanCount)), built on first use after an upload
@@ -179,9 +180,11 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
     float4* surf = (float4*)(host + hdr.offSurf); int* kind = (int*)(host + hdr.offKind);
     uint32_t* orig = (uint32_t*)(host + hdr.offOrig);
     SceneExtent extent; memset(&extent, 0, sizeof extent);
+    cudaComputeSceneNonFinite = false;
     for (uint32_t j = 0; j < count; j++) {
         const VcrtSphere& s = spheres[order[j]];
         orig[j] = order[j];
+        if (!isfinite(s.center[0]) || !isfinite(s.center[1]) || !isfinite(s.center[2]) || !isfinite(s.radius)) cudaComputeSceneNonFinite = true;
         if (j < scanCount) {   // what the LBVH needs to know about the spheres it will hold
             const float r = fabsf(s.radius);
             for (int k = 0; k < 3; k++) {
@@ -629,6 +632,10 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     // DESIGN.md section 6); only a handful of spheres leaves the tree nothing to prune
     if (traversal == VCRT_TRAVERSAL_AUTO)
         traversal = (cudaComputeSceneHeader.count <= kBruteForceLimit && (scanUFits(1024, 1, 30) || scanFits(256, 2, 12))) ? VCRT_TRAVERSAL_BRUTE : VCRT_TRAVERSAL_LBVH;
+    // A NaN centre or radius makes hit_sphere accept the sphere with t = NaN (every comparison of functions.glsl:20-31 is false),
+    // after which the reference's result depends on the ORDER of the scan; an infinite one poisons the filter / the boxes.
+    // Such scenes are rendered by the in-order exhaustive kernel, whatever was asked for.
+    if (cudaComputeSceneNonFinite && (traversal == VCRT_TRAVERSAL_BRUTE || traversal == VCRT_TRAVERSAL_LBVH)) traversal = VCRT_TRAVERSAL_SIMPLE;
     if (traversal == VCRT_TRAVERSAL_BRUTE && !scanFits(256, 2, 12) && !scanUFits(512, 2, 30))
         return fail(VCRT_ERROR_UNSUPPORTED, "scene does not fit shared memory for VCRT_TRAVERSAL_BRUTE%s", "");
     if (traversal > VCRT_TRAVERSAL_SIMPLE) return fail(VCRT_ERROR_INVALID_ARGUMENT, "unknown traversal%s", "");

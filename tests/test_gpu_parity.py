@@ -387,3 +387,37 @@ def test_pathological_inputs_follow_the_reference_arithmetic(oracle, vcrt, case)
             assert again.shape == gpu.shape
     finally:
         host.destroy()
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_randomised_scenes_cameras_and_parameters(oracle, vcrt, seed):
+    # 40 seeded draws over everything a caller controls: sphere count, sizes (incl. the always-tested > 50 class), materials with
+    # fuzz > 1 and ior <= 1 or 0, colours outside [0,1], camera, field of view, image shape, depth, spp, seed, sample offset
+    rng = np.random.default_rng(1000 + seed)
+    count = int(rng.choice([1, 2, 3, 7, 33, 64, 65, 150, 400]))
+    scene = random_scene(rng, count, big=int(rng.integers(0, min(4, count))))
+    scene[:, 0:3] *= rng.choice([0.01, 1.0, 30.0])
+    scene[:, 3] *= rng.choice([0.1, 1.0, 3.0])
+    scene[:, 4:7] = rng.uniform(-0.5, 2.0, (count, 3))
+    scene[:, 8] = np.where(scene[:, 7] == 3, rng.choice([0.0, 0.5, 1.0, 1.5, 2.4], count), rng.uniform(0, 3, count))
+    eye = rng.uniform(-15, 15, 3); at = rng.uniform(-2, 2, 3); up = rng.normal(0, 1, 3)
+    cam = cabi.VcrtCamera((ctypes.c_float * 3)(*eye), (ctypes.c_float * 3)(*at), (ctypes.c_float * 3)(*up), float(rng.uniform(1, 170)))
+    w, h = int(rng.integers(1, 130)), int(rng.integers(1, 90))
+    spp, depth = int(rng.integers(1, 6)), int(rng.choice([1, 2, 5, 50]))
+    rs, off = int(rng.integers(0, 2 ** 63)), int(rng.integers(0, 10 ** 6))
+    host.upload_scene(scene, cam)
+    try:
+        cpu, cst = oracle.render(scene, w, h, spp, depth=depth, seed=rs, sample_offset=off, camera=host.camera_array(cam))
+        for traversal in (SIMPLE, BRUTE, LBVH):
+            gpu, st = host.render(w, h, spp, depth=depth, seed=rs, sample_offset=off, traversal=traversal, sample_chunks=1)
+            assert st.rays == cst["rays"] and st.depthExhausted == cst["exhausted"], (traversal, count, w, h, spp, depth)
+            assert np.array_equal(gpu, cpu, equal_nan=True), (traversal, count, w, h, spp, depth)
+        if seed % 2 == 0:                                                # the same draw in BOOK semantics
+            book, cb = oracle.render_book(scene, w, h, spp, depth=depth, seed=rs, sample_offset=off, camera=host.camera_array(cam))
+            for traversal in (SIMPLE, BRUTE, LBVH):
+                gb, sb = host.render(w, h, spp, depth=depth, seed=rs, sample_offset=off, traversal=traversal, sample_chunks=1,
+                                     semantics=cabi.VCRT_SEMANTICS_BOOK)
+                assert sb.rays == cb["rays"] and sb.depthExhausted == cb["exhausted"], (traversal, count, w, h, spp, depth)
+                assert np.array_equal(gb, book, equal_nan=True), (traversal, count, w, h, spp, depth)
+    finally:
+        host.destroy()

@@ -677,6 +677,15 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         plan.lastBandFirst = fullBands << VCRT_BAND_SHIFT; plan.lastBandPixels = plan.pixelsPadded - plan.lastBandFirst;
         plan.invRuns = plan.runsPerPixel ? nextafterf(1.0f / (float)plan.runsPerPixel, 0.f) : 0.f;
         plan.invLastBand = plan.lastBandPixels ? nextafterf(1.0f / (float)plan.lastBandPixels, 0.f) : 0.f;
+        plan.tiles = plan.pixelsPadded / 32u; plan.invTiles = nextafterf(1.0f / (float)plan.tiles, 0.f);
+        plan.tileStride = 1u;
+        if (traversal == VCRT_TRAVERSAL_BRUTE && fullBands >= 1u) {
+            uint32_t stride = plan.tiles / (kBandPixels / 32u);
+            if (stride > 31u) stride = 31u;                       // (tile index * stride) stays below 2^31
+            auto gcd = [](uint32_t a, uint32_t b) { while (b) { uint32_t t = a % b; a = b; b = t; } return a; };
+            while (stride > 1u && gcd(stride, plan.tiles) != 1u) stride--;
+            plan.tileStride = stride;
+        }
     }
     rc = ensureImageBuffers(p->width, p->height, chunks); if (rc) return rc;
     const bool keep = (p->flags & VCRT_FLAG_ACCUMULATE) && cudaComputeAccumulatedSamples > 0;

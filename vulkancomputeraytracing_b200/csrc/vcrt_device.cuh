@@ -95,7 +95,9 @@ struct Frame { V3 center, pixel00, du, dv; };
 // Items are numbered band by band: all runs of the first kBandPixels pixels, then all runs of the next band, ...  The
 // paths in flight (3e5 per GPU) then touch a few MB of the accumulation buffer at a time, which stays in L2; numbering
 // sample-major instead sweeps the whole buffer once per sample and made L2 write every RED through to DRAM (29.7 GB per
-// C2 launch against 33 MB of image, profiles/traffic.json).
+// C2 launch against 33 MB of image, profiles/traffic.json).  For the brute-force kernels a band is spread over the whole image
+// (tileStride): a band of neighbouring tiles is all sky or all spheres, so the share of slots that need a new sample per
+// round swings from band to band and the shading phases overlap the scans less well (measured 0.8 %).
 #ifndef VCRT_BAND_SHIFT
 #define VCRT_BAND_SHIFT 18
 #endif
@@ -110,6 +112,9 @@ struct ItemPlan {
     uint32_t lastBandFirst;   // first padded pixel of the last, short band
     uint32_t lastBandPixels;  // its size (may be 0)
     float invRuns, invLastBand;   // reciprocals, rounded down, for the float-estimate divisions
+    uint32_t tileStride;      // consecutive tiles of the numbering are this many tiles apart in the image (coprime with the tile count)
+    uint32_t tiles;           // pixelsPadded / 32
+    float invTiles;
 };
 
 struct RenderArgs {
@@ -151,6 +156,11 @@ __device__ __forceinline__ void item_to_run(const ItemPlan& plan, uint32_t id, u
     } else {                                                   // the last, short band
         chunk = udiv_small(id - plan.lastBandFirst * plan.runsPerPixel, plan.lastBandPixels, plan.invLastBand, pid);
         pid += plan.lastBandFirst;
+    }
+    if (plan.tileStride > 1u) {   // spread a band over the whole image: tile t of the numbering is tile (t * stride) mod tiles of the image
+        uint32_t tile;
+        udiv_small((pid >> 5) * plan.tileStride, plan.tiles, plan.invTiles, tile);
+        pid = (tile << 5) | (pid & 31u);
     }
 }
 

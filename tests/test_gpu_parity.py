@@ -311,7 +311,7 @@ def test_both_lbvh_kernel_generations_agree(oracle, vcrt):
                 assert sb.rays == cb["rays"] and sb.depthExhausted == cb["exhausted"] and np.array_equal(gb, book)
             nested, sn = host.render(203, 113, 5, traversal=LBVH, shape=31)
             flat, sf = host.render(203, 113, 5, traversal=LBVH)
-            assert sf.rays == sn.rays and sf.nodeVisits == sn.nodeVisits and np.array_equal(flat, nested)
+            assert sf.rays == sn.rays and 0 < sf.nodeVisits <= sn.nodeVisits and np.array_equal(flat, nested)   # the flat kernel widens its boxes less
         finally:
             host.destroy()
 

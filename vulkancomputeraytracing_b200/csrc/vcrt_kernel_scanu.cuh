@@ -55,7 +55,10 @@ VCRT_DEV void flag_if_ge(uint32_t& m, float q, float s, uint32_t bit) {
     asm("{\n\t.reg .pred p;\n\tsetp.ge.f32 p, %1, %2;\n\t@p or.b32 %0, %0, %3;\n\t}" : "+r"(m) : "f"(q), "f"(s), "r"(bit));
 }
 
-template <int THREADS, int PAIRS, int LCAP, bool FIXED, int UNROLL = 16>
+#ifndef VCRT_SCANU_UNROLL
+#define VCRT_SCANU_UNROLL 16   // spheres per unrolled scan body (32 measured: see DESIGN.md 6.1)
+#endif
+template <int THREADS, int PAIRS, int LCAP, bool FIXED, int UNROLL = VCRT_SCANU_UNROLL>
 __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned char* __restrict__ blobGlobal, RenderArgs args, int scanPad) {
     using Cfg = ScanUConfig<THREADS, PAIRS, LCAP>;
     constexpr int R = Cfg::R;

@@ -243,6 +243,49 @@ def test_lbvh_bit_exact_on_scaled_scenes(oracle, vcrt, grid):
         host.destroy()
 
 
+def far_field_scene(case):
+    rng = np.random.default_rng(zlib.crc32(case.encode()))
+    n = 20000 if case in ("slab_3000", "slab_3000_ground", "tiny_radii") else 3000
+    s = np.zeros((n, 10), np.float32)
+    s[:, 4:7] = rng.uniform(0.3, 1, (n, 3)); s[:, 7] = rng.integers(1, 4, n)
+    s[:, 8] = np.where(s[:, 7] == 3, 1.5, rng.uniform(0, 1, n))
+    eye, at, fov = (0, 2, 0), (100, 1.5, 30), 60.0
+    if case.startswith("slab_3000"):     # L up to 4000: 19 eps L^2 = 18 against r^2 = 1 .. 36
+        s[:, 0] = rng.uniform(-3000, 3000, n); s[:, 1] = rng.uniform(0, 12, n); s[:, 2] = rng.uniform(-3000, 3000, n); s[:, 3] = rng.uniform(1, 6, n)
+        if case.endswith("ground"): s[0] = [0, -1000, 0, 1000, .5, .5, .5, 1, 1.0, 0]
+    elif case == "cube_800":
+        s[:, 0:3] = rng.uniform(-800, 800, (n, 3)); s[:, 3] = rng.uniform(0.5, 8, n)
+        eye, at = (10, 20, -30), (400, 100, 300)
+    elif case == "far_camera":           # the whole scene is far from the origin of every primary ray
+        s[:, 0:3] = rng.uniform(-40, 40, (n, 3)); s[:, 3] = rng.uniform(0.2, 1.0, n)
+        eye, at, fov = (2500, 300, -1800), (0, 0, 0), 3.0
+    else:                                # radii far below the error of the discriminant: what is "hit" is decided by rounding
+        s[:, 0] = rng.uniform(-400, 400, n); s[:, 1] = rng.uniform(0, 3, n); s[:, 2] = rng.uniform(-400, 400, n); s[:, 3] = rng.uniform(0.02, 0.1, n)
+        eye, at, fov = (-390, 1.5, -390), (400, 1.5, 400), 40.0
+    cam = cabi.VcrtCamera((ctypes.c_float * 3)(*eye), (ctypes.c_float * 3)(*at), (ctypes.c_float * 3)(0, 1, 0), fov)
+    return s, cam
+
+
+@pytest.mark.parametrize("case", ["slab_3000", "slab_3000_ground", "cube_800", "far_camera", "tiny_radii"])
+def test_lbvh_widening_is_conservative_in_the_far_field(vcrt, case):
+    # At a distance L the reference's binary32 discriminant is off by ~19 eps L^2, so far spheres are "hit" by rays that miss them
+    # (L = 3000: 19 eps L^2 = 10).  The LBVH must still reach every sphere the exact test accepts: its boxes are widened per ray by
+    # a bound on that error (vcrt_kernel_lbvh.cuh, distance-aware widening).  The exhaustive in-order kernel tests every sphere
+    # exactly for every ray, so a sphere the tree misses shows up as a different bit.
+    s, cam = far_field_scene(case)
+    host.upload_scene(s, cam)
+    try:
+        for depth in (1, 12):
+            simple, ss = host.render(480, 270, 2, depth=depth, traversal=SIMPLE, sample_chunks=1)
+            tree, st = host.render(480, 270, 2, depth=depth, traversal=LBVH, sample_chunks=1)
+            assert ss.rays == st.rays and np.array_equal(simple, tree)
+            nested, sn = host.render(480, 270, 2, depth=depth, traversal=LBVH, sample_chunks=1, shape=31)   # first generation: L = F, K = 64 eps
+            assert np.array_equal(nested, tree) and st.nodeVisits <= sn.nodeVisits
+        assert ss.rays - 480 * 270 * 2 > 1000                     # enough hits for the comparison to mean something
+    finally:
+        host.destroy()
+
+
 def test_lbvh_duplicates_and_coincident_centres(oracle, vcrt):
     # identical spheres (exact ties: the lower index must win, as in the reference's in-order scan), concentric shells
     rng = np.random.default_rng(5)

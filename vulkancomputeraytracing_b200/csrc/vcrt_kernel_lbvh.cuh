@@ -14,9 +14,19 @@
         a sphere can pass the exact test only if the distance D from its centre to the ray's line
         satisfies D^2 <= r^2 + ~18 eps (|o-c|^2 + r^2) (rounding of oc, the two dot products, a*c).
         Every box is therefore widened per ray by `grow` >= sqrt(r^2 + K) - r with
-        K = 64 eps (L^2 + rmax^2), L >= |o - c| for every sphere this ray can still accept, plus
+        K = 32 eps (L^2 + rmax^2), L >= |o - c| for every sphere this ray can still accept, plus
         16 eps (|o| + F) for the rounding of the slab arithmetic itself (F = the largest |o - c|
         over the whole tree).
+        Where 32 comes from (u = eps = 2^-24, every operation of hit_ordered rounded once, L = |o - c|):
+        oc = (o - c)(1 + u);  |half_b - (o-c).d| <= 4u L|d|;  |fl(oc.oc) - L^2| <= 5u L^2;
+        |cc - (L^2 - r^2)| <= 6u L^2 + 2u r^2;  |fl(half_b^2) - ((o-c).d)^2| <= 9u a L^2;
+        |fl(a cc) - a(L^2 - r^2)| <= a (10u L^2 + 6u r^2);  the last subtraction keeps the sign.  So
+        disc >= 0 needs D^2 <= r^2 + 19u L^2 + 6u r^2, which puts the point of closest approach inside
+        the sphere's box inflated by sqrt(r^2 + K19) - r.  The traversal also needs the ACCEPTED point
+        p(t_s) inside every inflated ancestor box (so that n <= t_s <= rec.t and f >= t_s > 0):
+        (t_s - t_c)|d| <= 9u L + sqrt(r^2 - D^2 + K19)(1 + 5u) gives |p(t_s) - c|^2 <= r^2 + 28u L^2 + 26u r^2.
+        32 covers both with room for the second-order terms.  (The first-generation kernel keeps 64
+        and L = F.)
         Distance-aware widening (second-generation kernel): L = F is always valid but wasteful - at
         100 k spheres F = 230 and grow = 0.46 on spheres of radius 0.2, so every box was 3.3x too
         wide.  A sphere is only accepted with a computed root <= t0 (the best root so far: the
@@ -236,6 +246,11 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_kernel(BvhScene 
 #define LBVH_OCT 1
 #endif
 
+#ifndef LBVH_K_EPS
+#define LBVH_K_EPS 32.0f
+#endif
+constexpr float kLbvhK = LBVH_K_EPS * 5.9604644775390625e-08f;   // K = 32 eps (L^2 + rmax^2), eps = 2^-24 (file header)
+
 VCRT_DEV float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 VCRT_DEV float sqrt_approx(float x) { float r; asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
@@ -275,7 +290,7 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
     // grows with L^2, so near the origin the boxes stay tight: at 100 k spheres F = 230 gives 0.46 on spheres of radius 0.2,
     // while a ray that meets the ground 20 units away needs 0.004.
     const float sqrtF = sqrt_approx(F2);
-    const float sqrtKF = sqrt_approx(3.814697265625e-06f * (F2 + rr));
+    const float sqrtKF = sqrt_approx(kLbvhK * (F2 + rr));
     float widen = fminf(sqrtKF, sqrtKF * sqrtKF * scene.halfInvRadiusMin);   // with L = F
     if (widen > 0.05f * scene.radiusMin) {   // a small scene needs no refinement (485 spheres: 3.7 % of the radius)
         const float E = scene.radiusMax + sqrtKF;
@@ -284,7 +299,7 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
         const float ez = uz ? ((pz_ ? scene.centreMax.z + E : scene.centreMin.z - E) - ray.o.z) * iz : kInf;
         const float tStar = fminf(rec.t, fmaxf(fminf(fminf(ex, ey), ez), 0.f));
         const float L = fminf(sqrtF, fmaf(1.01f * tStar, sqrt_approx(a), fmaf(2.1f, scene.radiusMax, 1.01f * E)));
-        const float K = 3.814697265625e-06f * fmaf(L, L, rr);
+        const float K = kLbvhK * fmaf(L, L, rr);
         widen = fminf(sqrt_approx(K), K * scene.halfInvRadiusMin);
     }
     // the bound only has to be conservative, so it is built from the approximate unit's sqrt / rcp (relative error <= 2^-22,

@@ -46,7 +46,7 @@ typedef struct RendererConfiguration {
     uint64_t seed;
     int32_t device;
     const char* sceneFile;         /* optional GLSL-text scene (globals.glsl:31-517 form) instead of the generator */
-    const char* outputPrefix;      /* "<prefix>.pfm" (linear) and "<prefix>.ppm" (sRGB-encoded) are written at the end; NULL = none */
+    const char* outputPrefix;      /* "<prefix>.pfm" (linear), "<prefix>.ppm" and "<prefix>.png" (sRGB-encoded) are written at the end; NULL = none */
 } RendererConfiguration;
 
 extern RendererConfiguration rendererConfiguration;

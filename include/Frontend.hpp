@@ -22,5 +22,7 @@ VkResult FrontendAcquireImage(void);
 VkResult FrontendWritePfm(IN const char* path);
 /* 8-bit image through the linear->sRGB transfer the reference's B8G8R8A8_SRGB swapchain applies (Frontend.cpp:43). */
 VkResult FrontendWritePpm(IN const char* path);
+/* The same 8-bit image as a PNG (stored deflate blocks, no compression library; carries an sRGB chunk). */
+VkResult FrontendWritePng(IN const char* path);
 
 #endif

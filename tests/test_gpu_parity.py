@@ -216,7 +216,14 @@ def test_host_program_end_to_end(tmp_path, oracle):
     cpu, _ = oracle.render(oracle.scene(), 96, 54, 4)
     assert np.abs(pfm - cpu[..., :3]).max() <= 2.0 ** -22       # 2 progressive frames of 2 spp == 4 spp
     with open(prefix + ".ppm", "rb") as f:
-        assert f.readline() == b"P6\n"
+        assert f.readline() == b"P6\n" and f.readline() == b"96 54\n" and f.readline() == b"255\n"
+        ppm = f.read()
+    with open(prefix + ".png", "rb") as f:                      # the same 8 bits in a PNG (stored deflate blocks)
+        png = f.read()
+    assert png[:8] == b"\x89PNG\r\n\x1a\n"
+    idat = png.index(b"IDAT")
+    rows = np.frombuffer(zlib.decompress(png[idat + 4:-16]), np.uint8).reshape(54, 1 + 96 * 3)
+    assert rows[:, 1:].tobytes() == ppm
 
 
 @pytest.mark.parametrize("grid", [50, 158])

@@ -84,7 +84,7 @@ int main(int argc, char** argv)
     if (rendererConfiguration.outputPrefix) {
         const std::string prefix = rendererConfiguration.outputPrefix;
         if (FrontendAcquireImage() != VK_SUCCESS || FrontendWritePfm((prefix + ".pfm").c_str()) != VK_SUCCESS ||
-            FrontendWritePpm((prefix + ".ppm").c_str()) != VK_SUCCESS) {
+            FrontendWritePpm((prefix + ".ppm").c_str()) != VK_SUCCESS || FrontendWritePng((prefix + ".png").c_str()) != VK_SUCCESS) {
             cerr << "Cannot write the image." << endl;
             EndRenderingOperation();
             return -1;

@@ -58,8 +58,11 @@ struct BvhScene {
     const float4* surf;
     const int* kind;
     const uint32_t* origIndex;
-    uint32_t treeCount;           // spheres in the tree = device indices [0, treeCount)
-    uint32_t count;               // all spheres; [treeCount, count) are tested for every ray
+    uint32_t treeCount;           // spheres in the tree
+    uint32_t count;               // all spheres
+    uint32_t scanCount;           // device indices [0, scanCount) and [scanCount, count) are each in the caller's order
+    const uint32_t* extra;        // device indices of the spheres outside the tree (outliers, then the always list): tested for every ray
+    uint32_t extraCount;
     float3 centreMin, centreMax;  // bounding box of the tree spheres' centres
     float radiusMin, radiusMax;   // over the tree spheres
     float halfInvRadiusMin;       // >= 1 / (2 radiusMin), rounded up
@@ -129,16 +132,16 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_kernel(BvhScene 
                     HitRec h; h.t = kTMax; h.index = -1;
                     // original order = ascending origIndex; device order differs only by moving the always list to the end,
                     // so walk both runs merged by original index
-                    uint32_t i = 0, j = scene.treeCount;
-                    while (i < scene.treeCount || j < scene.count) {
-                        const bool takeTree = j >= scene.count || (i < scene.treeCount && scene.origIndex[i] < scene.origIndex[j]);
+                    uint32_t i = 0, j = scene.scanCount;
+                    while (i < scene.scanCount || j < scene.count) {
+                        const bool takeTree = j >= scene.count || (i < scene.scanCount && scene.origIndex[i] < scene.origIndex[j]);
                         const uint32_t k = takeTree ? i++ : j++;
                         hit_exact(scene.shape[k], (int)k, ray, a, h);
                         nTests++;
                     }
                     rec.t = h.t; rec.device = h.index;
                 } else {
-                    for (uint32_t k = scene.treeCount; k < scene.count; k++) { hit_ordered(__ldg(&scene.shape[k]), (int)k, __ldg(&scene.origIndex[k]), ray, a, rec); nTests++; }
+                    for (uint32_t x = 0; x < scene.extraCount; x++) { const uint32_t k = __ldg(&scene.extra[x]); hit_ordered(__ldg(&scene.shape[k]), (int)k, __ldg(&scene.origIndex[k]), ray, a, rec); nTests++; }
                     if (scene.treeCount == 1u) { hit_ordered(__ldg(&scene.leafShape[0]), (int)__ldg(&scene.leafDevice[0]), __ldg(&scene.leafOrig[0]), ray, a, rec); nTests++; }
                     else if (scene.treeCount > 1u) {
                         // per-ray widening of every box (file header)
@@ -261,9 +264,9 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
     const bool degenerate = !(a > 1e-30f && a < 1e30f && oo < 1e30f);
     if (degenerate) {   // the reference's in-order scan, literally (see render_lbvh_kernel)
         HitRec h; h.t = kTMax; h.index = -1;
-        uint32_t i = 0, j = scene.treeCount;
-        while (i < scene.treeCount || j < scene.count) {
-            const bool takeTree = j >= scene.count || (i < scene.treeCount && scene.origIndex[i] < scene.origIndex[j]);
+        uint32_t i = 0, j = scene.scanCount;
+        while (i < scene.scanCount || j < scene.count) {
+            const bool takeTree = j >= scene.count || (i < scene.scanCount && scene.origIndex[i] < scene.origIndex[j]);
             const uint32_t k = takeTree ? i++ : j++;
             hit_exact(scene.shape[k], (int)k, ray, a, h);
             n.tests++;
@@ -271,7 +274,7 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
         rec.t = h.t; rec.device = h.index;
         return;
     }
-    for (uint32_t k = scene.treeCount; k < scene.count; k++) { hit_ordered(__ldg(&scene.shape[k]), (int)k, __ldg(&scene.origIndex[k]), ray, a, rec); n.tests++; }
+    for (uint32_t x = 0; x < scene.extraCount; x++) { const uint32_t k = __ldg(&scene.extra[x]); hit_ordered(__ldg(&scene.shape[k]), (int)k, __ldg(&scene.origIndex[k]), ray, a, rec); n.tests++; }
     if (scene.treeCount == 1u) { hit_ordered(__ldg(&scene.leafShape[0]), (int)__ldg(&scene.leafDevice[0]), __ldg(&scene.leafOrig[0]), ray, a, rec); n.tests++; }
     if (scene.treeCount <= 1u) return;
     // per-ray widening of every box and the slab constants: as in render_lbvh_kernel

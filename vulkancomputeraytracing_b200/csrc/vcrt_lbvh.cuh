@@ -16,7 +16,8 @@
     A node keeps the boxes of BOTH children (64 bytes, four 16-byte loads) so one visit decides two
     subtrees.  Leaves are single spheres, stored in sorted order next to their original index.
 
-    Spheres with a radius above kAlwaysRadius (the ground) are not in the tree; every ray tests them first.
+    Spheres with a radius above kAlwaysRadius (the ground) and a few outliers much larger than the rest are not
+    in the tree; every ray tests them first (ensureBvh in vcrt_cabi.cu picks them).
 */
 #pragma once
 #include "vcrt_shade.cuh"
@@ -35,8 +36,9 @@ struct BvhNode {
 // layout, each child's NEAR planes where BvhNode has the minimum and its FAR planes where BvhNode has the maximum, so a
 // ray picks its planes once (one base pointer) instead of with 12 selects per visit.
 struct BvhBuildArgs {
-    const float4* shape;        // device-order (cx, cy, cz, r); the first `count` entries go into the tree
+    const float4* shape;        // device-order (cx, cy, cz, r)
     const uint32_t* origIndex;  // device index -> index in the caller's array
+    const uint32_t* treeIndex;  // [count] device indices of the spheres that go into the tree (ascending)
     uint32_t count;
     float3 boxMin, boxInvExtent;   // centre bounding box -> [0,1)^3
     unsigned long long* keys;      // [count]
@@ -61,12 +63,13 @@ VCRT_DEV uint32_t expand_bits10(uint32_t v) {   // 10 bits -> every third bit
 __global__ void lbvh_keys_kernel(BvhBuildArgs g) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.count) return;
-    float4 s = g.shape[i];
+    const uint32_t device = g.treeIndex[i];
+    float4 s = g.shape[device];
     float x = fminf(fmaxf((s.x - g.boxMin.x) * g.boxInvExtent.x * 1024.f, 0.f), 1023.f);
     float y = fminf(fmaxf((s.y - g.boxMin.y) * g.boxInvExtent.y * 1024.f, 0.f), 1023.f);
     float z = fminf(fmaxf((s.z - g.boxMin.z) * g.boxInvExtent.z * 1024.f, 0.f), 1023.f);
     uint32_t code = (expand_bits10((uint32_t)x) << 2) | (expand_bits10((uint32_t)y) << 1) | expand_bits10((uint32_t)z);
-    g.keys[i] = ((unsigned long long)code << 32) | i;
+    g.keys[i] = ((unsigned long long)code << 32) | device;
 }
 
 // Leaf boxes: centre -+ radius, rounded outward.  (The per-ray margin that makes the box test conservative against

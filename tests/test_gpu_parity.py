@@ -293,6 +293,30 @@ def test_lbvh_widening_is_conservative_in_the_far_field(vcrt, case):
         host.destroy()
 
 
+@pytest.mark.parametrize("case", ["forty_large", "equal_large", "few_spheres", "all_large_but_one"])
+def test_lbvh_outlier_spheres_outside_the_tree(oracle, vcrt, case):
+    # Spheres much larger than the median radius are kept out of the tree (at most 16, the largest first) and tested exactly
+    # for every ray; the image must not depend on which side of that policy a sphere falls.
+    rng = np.random.default_rng(zlib.crc32(case.encode()))
+    n, large = {"forty_large": (240, 40), "equal_large": (240, 40), "few_spheres": (20, 3), "all_large_but_one": (60, 0)}[case]
+    s = random_scene(rng, n)
+    s[:, 3] = rng.uniform(0.08, 0.15, n)
+    pick = rng.choice(n, large, replace=False)                     # scattered through the caller's order
+    s[pick, 3] = 1.5 if case == "equal_large" else rng.uniform(0.8, 2.5, large)
+    if case == "all_large_but_one":
+        s[:, 3] = rng.uniform(1.0, 2.0, n); s[7, 3] = 0.01         # the median is large: nothing counts as an outlier
+    cam = cabi.VcrtCamera((ctypes.c_float * 3)(0, 1, 14), (ctypes.c_float * 3)(0, 0, 0), (ctypes.c_float * 3)(0, 1, 0), 50.0)
+    host.upload_scene(s, cam)
+    try:
+        cpu, cst = oracle.render(s, 120, 80, 2, depth=16, camera=host.camera_array(cam))
+        gpu, st = host.render(120, 80, 2, depth=16, traversal=LBVH, sample_chunks=1)
+        assert_same(gpu, st, cpu, cst)
+        nested, _ = host.render(120, 80, 2, depth=16, traversal=LBVH, sample_chunks=1, shape=31)
+        assert np.array_equal(nested, gpu)
+    finally:
+        host.destroy()
+
+
 def test_lbvh_duplicates_and_coincident_centres(oracle, vcrt):
     # identical spheres (exact ties: the lower index must win, as in the reference's in-order scan), concentric shells
     rng = np.random.default_rng(5)

@@ -434,7 +434,8 @@ def test_item_numbering_corner_cases(oracle, gpu_scene):
         assert sg.rays == cst["rays"] and np.abs(gpu - cpu).max() <= 2.0 ** -20
 
 
-@pytest.mark.parametrize("case", ["zero_and_negative_radius", "tiny_and_huge", "nan_and_inf_spheres", "degenerate_camera", "coincident_centres"])
+@pytest.mark.parametrize("case", ["zero_and_negative_radius", "tiny_and_huge", "nan_and_inf_spheres", "degenerate_camera", "coincident_centres",
+                                  "nan_spheres_after_a_huge_first_sphere", "beyond_the_tame_range", "edge_of_the_tame_range"])
 def test_pathological_inputs_follow_the_reference_arithmetic(oracle, vcrt, case):
     # inputs the reference never guards against: whatever binary32 arithmetic makes of them, all traversals make the same
     rng = np.random.default_rng(zlib.crc32(case.encode()))
@@ -448,6 +449,24 @@ def test_pathological_inputs_follow_the_reference_arithmetic(oracle, vcrt, case)
         scene[0, 0] = np.nan; scene[1, 3] = np.inf; scene[2, 1] = -np.inf; scene[3, 3] = np.nan; scene[4, 4:7] = np.nan
     elif case == "degenerate_camera":
         cam = cabi.VcrtCamera((ctypes.c_float * 3)(1, 2, 3), (ctypes.c_float * 3)(1, 2, 3), (ctypes.c_float * 3)(0, 1, 0), 50.0)   # lookfrom == lookat
+    elif case == "nan_spheres_after_a_huge_first_sphere":
+        # a NaN sphere is "hit" at t = NaN and from then on the LAST sphere of the caller's order with a root > t_min wins: the layer
+        # keeps spheres of radius > 50 at the end of its own arrays, which must not change that order
+        scene[0] = [0, -1000, 0, 1000, .5, .5, .5, 1, 1.0, 0]; scene[3] = [0, 0, -300, 200, .9, .2, .2, 2, 0.1, 0]
+        scene[7, 0] = np.nan; scene[20, 3] = np.nan
+    elif case == "beyond_the_tame_range":
+        # finite spheres whose squares overflow: disc = inf - inf = NaN, the sphere is "hit" at t = NaN like a NaN sphere.  The filter and
+        # the tree are only conservative against rounding, so such a scene goes to the in-order kernel whatever was asked for
+        scene[0] = [0, -1000, 0, 1000, .5, .5, .5, 2, 0.0, 0]; scene[1] = [0, 0, -300, 200, .9, .2, .2, 2, 0.1, 0]
+        scene[4:6, 0:3] *= 1e17; scene[6, 3] = 3e18; scene[8:12, 0:3] = [[3e38, 0, 0], [0, 3e38, 1], [1e30, 1e30, 1e30], [-3e38, 1, 1]]
+        scene[8:12, 7] = 2
+    elif case == "edge_of_the_tame_range":
+        # a cluster around a point with |p|^2 = 1e18 (t_max = 1e5 keeps anything farther than 1.35e6 from a ray's origin invisible): hit
+        # points land on both sides of |o|^2 = 1e18, where rays switch to the exhaustive scan inside the kernels
+        base = np.array([7.0710678e8, 7.0710678e8, 0.0])
+        scene[:, 0:3] = base + rng.uniform(-8e5, 8e5, (40, 3)); scene[:, 3] = rng.uniform(5e4, 3e5, 40)
+        eye = base + [0, 1e5, 1.2e6]
+        cam = cabi.VcrtCamera((ctypes.c_float * 3)(*eye), (ctypes.c_float * 3)(*base), (ctypes.c_float * 3)(0, 1, 0), 50.0)
     else:
         scene[0:20, 0:3] = scene[0, 0:3]; scene[0:20, 3] = np.linspace(0.5, 1.5, 20)   # 20 concentric spheres of three materials
     host.upload_scene(scene, cam)
@@ -455,6 +474,7 @@ def test_pathological_inputs_follow_the_reference_arithmetic(oracle, vcrt, case)
         cpu, cst = oracle.render(scene, 64, 48, 2, depth=12, camera=host.camera_array(cam))
         for traversal in (SIMPLE, BRUTE, LBVH):
             gpu, st = host.render(64, 48, 2, depth=12, traversal=traversal, sample_chunks=1)
+            assert st.traversalUsed == (SIMPLE if case in ("tiny_and_huge", "nan_and_inf_spheres", "nan_spheres_after_a_huge_first_sphere", "beyond_the_tame_range") else traversal)
             assert st.rays == cst["rays"] and st.depthExhausted == cst["exhausted"], (traversal, st.rays, cst["rays"])
             assert np.array_equal(gpu, cpu, equal_nan=True), traversal
             again, _ = host.render(64, 48, 2, depth=12, traversal=traversal)          # fixed-point accumulation must not trap on NaN either

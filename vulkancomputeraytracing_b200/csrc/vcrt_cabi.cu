@@ -39,7 +39,7 @@ static unsigned char* cudaComputeSceneBlob = nullptr;   // device copy of the So
 static SceneBlob cudaComputeSceneHeader;
 static bool cudaComputeSceneReady = false;
 static bool cudaComputeSceneInConstant = false;   // the filter table of the uniform-datapath scan is loaded
-static bool cudaComputeSceneNonFinite = false;    // a centre or radius is NaN / inf: only the in-order scan reproduces the reference
+static bool cudaComputeSceneNonFinite = false;    // a centre or radius is NaN / inf / beyond the tame range (vcrt_device.cuh): only the in-order scan reproduces the reference
 struct SceneExtent { float centreMin[3], centreMax[3], radiusMin, radiusMax; };
 // LBVH over the scan spheres (device indices [0, scanCount)), built on first use after an upload
 static bool cudaComputeBvhReady = false;
@@ -165,6 +165,10 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
         kept = 0;
         for (uint32_t i = 0; i < count; i++) if (spheres[i].radius > kAlwaysRadius && kept < kMaxAlways) { order[scanCount + alwaysCount++] = i; kept++; }
     }
+    // The device arrays keep the huge spheres at the END.  That must not change the order the reference scans in (equal roots go
+    // to the lower index; with NaNs about, everything depends on the order), so the split is only made when they already close
+    // the caller's array, as the ground of SceneGenerator.cpp:52 does; otherwise every sphere is scanned like any other.
+    for (uint32_t j = 0; j < count; j++) if (order[j] != j) { for (uint32_t i = 0; i < count; i++) order[i] = i; scanCount = count; alwaysCount = 0; break; }
     const uint32_t scanPad = (scanCount + 15u) & ~15u;   // the scan walks the list 16 (first generation: 8) spheres at a time
 
     SceneBlob hdr; memset(&hdr, 0, sizeof hdr);
@@ -184,7 +188,9 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
     for (uint32_t j = 0; j < count; j++) {
         const VcrtSphere& s = spheres[order[j]];
         orig[j] = order[j];
-        if (!isfinite(s.center[0]) || !isfinite(s.center[1]) || !isfinite(s.center[2]) || !isfinite(s.radius)) cudaComputeSceneNonFinite = true;
+        // (negated comparisons: a NaN lands here too)
+        if (!(fabsf(s.center[0]) <= kTameSceneMax && fabsf(s.center[1]) <= kTameSceneMax && fabsf(s.center[2]) <= kTameSceneMax && fabsf(s.radius) <= kTameSceneMax))
+            cudaComputeSceneNonFinite = true;
         shape[j] = make_float4(s.center[0], s.center[1], s.center[2], s.radius);
         surf[j] = make_float4(s.colour[0], s.colour[1], s.colour[2], s.texture[1]);
         kind[j] = (int)s.texture[0];   // switch(int(record.texture.x)), textures.glsl:66

@@ -169,6 +169,14 @@ constexpr uint32_t kFlagCountStats = 1u << 3;   // VCRT_FLAG_COUNT_STATS of incl
 struct Ray { V3 o, d; };
 struct HitRec { float t; int index; };  // nearest accepted root and its sphere (index < 0: none)
 
+// The "tame" range.  The candidate filter and the LBVH boxes are conservative against the ROUNDING of the reference's exact
+// test; they say nothing once that test overflows (half_b^2 or a*c = inf, disc = NaN: the sphere is then "hit" at t = NaN and the
+// result depends on the order of the scan).  A ray with |d|^2 in (1e-20, 1e18) and |o|^2 < 1e18 against spheres with
+// |centre|, |radius| <= 1e9 keeps every intermediate below 3.7e37; every other ray takes the exhaustive in-order scan inside the
+// kernels, and a scene with a sphere outside that range is rendered by the in-order kernel altogether (cudaUploadScene).
+constexpr float kTameDirMin2 = 1e-20f, kTameMax2 = 1e18f, kTameSceneMax = 1e9f;
+VCRT_DEV bool tame_ray(float dd, float oo) { return dd > kTameDirMin2 && dd < kTameMax2 && oo < kTameMax2; }
+
 constexpr float kTMin = 0.001f;   // functions.glsl:75
 constexpr float kTMax = 1e5f;     // globals.glsl:26 `infinity`
 constexpr float kFixedOne = 4294967296.0f;   // 2^32: radiance sums are exact integers in units of 2^-32

@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_kernel(BvhScene 
                 const float a = vdot(ray.d, ray.d);
                 OrderedHit rec; rec.t = kTMax; rec.device = -1; rec.orig = 0xffffffffu;
                 const float oo = fmaf(ray.o.x, ray.o.x, fmaf(ray.o.y, ray.o.y, ray.o.z * ray.o.z));
-                const bool degenerate = !(a > 1e-30f && a < 1e30f && oo < 1e30f);
+                const bool degenerate = !tame_ray(a, oo);
                 if (degenerate) {   // the reference's in-order scan, literally
                     HitRec h; h.t = kTMax; h.index = -1;
                     // original order = ascending origIndex; device order differs only by moving the always list to the end,
@@ -261,7 +261,7 @@ struct LbvhCounts { uint32_t rays, nodes, tests, exhausted, bad; };
 
 VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, OrderedHit& rec, int* stack, LbvhCounts& n) {
     const float oo = fmaf(ray.o.x, ray.o.x, fmaf(ray.o.y, ray.o.y, ray.o.z * ray.o.z));
-    const bool degenerate = !(a > 1e-30f && a < 1e30f && oo < 1e30f);
+    const bool degenerate = !tame_ray(a, oo);
     if (degenerate) {   // the reference's in-order scan, literally (see render_lbvh_kernel)
         HitRec h; h.t = kTMax; h.index = -1;
         uint32_t i = 0, j = scene.scanCount;

@@ -78,7 +78,7 @@ VCRT_DEV FilterRay make_filter(const Ray& r) {
     FilterRay f;
     float len2 = fmaf(r.d.x, r.d.x, fmaf(r.d.y, r.d.y, r.d.z * r.d.z));
     float oo = fmaf(r.o.x, r.o.x, fmaf(r.o.y, r.o.y, r.o.z * r.o.z));
-    f.degenerate = !(len2 > 1e-30f && len2 < 1e30f && oo < 1e30f);
+    f.degenerate = !tame_ray(len2, oo);
     float inv = rsqrtf(len2);
     float dx = r.d.x * inv, dy = r.d.y * inv, dz = r.d.z * inv;
     float sign = copysignf(1.0f, dz);

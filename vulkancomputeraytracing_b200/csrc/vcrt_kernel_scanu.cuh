@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                         const float rx = STF(SF_DX, r), ry = STF(SF_DY, r), rz = STF(SF_DZ, r);
                         const float len2 = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
                         const float oo = fmaf(ox, ox, fmaf(oy, oy, oz * oz));
-                        if (!(len2 > 1e-30f && len2 < 1e30f && oo < 1e30f)) exhaustMask |= 1u << r;   // no usable filter for this ray
+                        if (!tame_ray(len2, oo)) exhaustMask |= 1u << r;   // no usable filter for this ray
                         else {
                             const float inv = rsqrtf(len2);
                             f[h][0] = rx * inv; f[h][1] = ry * inv; f[h][2] = rz * inv;

@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanw_kernel(const unsigned
                         const float rx = WSF(WF_DX, r, tid), ry = WSF(WF_DY, r, tid), rz = WSF(WF_DZ, r, tid);
                         const float len2 = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
                         const float oo = fmaf(ox, ox, fmaf(oy, oy, oz * oz));
-                        if (!(len2 > 1e-30f && len2 < 1e30f && oo < 1e30f)) exhaustMask |= 1u << r;   // no usable filter for this ray
+                        if (!tame_ray(len2, oo)) exhaustMask |= 1u << r;   // no usable filter for this ray
                         else {
                             const float inv = rsqrtf(len2);
                             f[h][0] = rx * inv; f[h][1] = ry * inv; f[h][2] = rz * inv;

@@ -293,6 +293,22 @@ def test_lbvh_widening_is_conservative_in_the_far_field(vcrt, case):
         host.destroy()
 
 
+@pytest.mark.parametrize("case", ["slab_3000", "cube_800", "far_camera"])
+def test_brute_force_filter_is_conservative_in_the_far_field(vcrt, case):
+    # the same scenes, thinned to what fits shared memory, through the candidate filter of the brute-force scan: its margin is
+    # relative (kappa (|c|^2 + |o|^2 + r^2)), so it has to hold where the reference's discriminant is dominated by rounding too
+    s, cam = far_field_scene(case)
+    s = s[:: max(1, s.shape[0] // 1500)][:1500]
+    host.upload_scene(s, cam)
+    try:
+        simple, ss = host.render(480, 270, 2, depth=12, traversal=SIMPLE, sample_chunks=1)
+        brute, sb = host.render(480, 270, 2, depth=12, traversal=BRUTE, sample_chunks=1)
+        assert sb.traversalUsed == BRUTE and sb.rays == ss.rays and np.array_equal(brute, simple)
+        assert sb.listOverflows < sb.rays // 2 and ss.rays - 480 * 270 * 2 > 300   # the filter ran for most rays (far_camera: its margin, 1.5e-5 |o|^2 = 145, passes so much that 16 % of the lists overflow), and something was hit
+    finally:
+        host.destroy()
+
+
 @pytest.mark.parametrize("case", ["forty_large", "equal_large", "few_spheres", "all_large_but_one"])
 def test_lbvh_outlier_spheres_outside_the_tree(oracle, vcrt, case):
     # Spheres much larger than the median radius are kept out of the tree (at most 16, the largest first) and tested exactly

@@ -88,15 +88,16 @@ enum {
 typedef struct VcrtRenderParams {
     uint32_t width;            /* IMAGE_WIDTH */
     uint32_t height;           /* IMAGE_HEIGHT */
-    uint32_t samplesPerPixel;  /* SAMPLES_PER_PIXEL rendered by THIS call on THIS device */
+    uint32_t samplesPerPixel;  /* SAMPLES_PER_PIXEL rendered by THIS call on THIS device (0: a rank that only joins the reduce) */
     uint32_t maxDepth;         /* MAX_RECURSION_LEVEL */
     uint64_t seed;             /* Philox key */
     uint32_t sampleOffset;     /* global index of this call's first sample (spp sharding / progressive) */
     uint32_t totalSamples;     /* divisor of the final image; 0 = samples accumulated so far (after reduce: over all ranks) */
     uint32_t traversal;        /* VCRT_TRAVERSAL_* */
     uint32_t flags;            /* VCRT_FLAG_* */
-    uint32_t sampleChunks;     /* 0 = auto; 1 = a pixel's samples are summed strictly in index order */
-    uint32_t reserved[2];      /* must be 0 (development switches) */
+    uint32_t sampleChunks;     /* 0 = auto (order-free 32.32 fixed-point sums); 1 = a pixel's samples are summed strictly in index
+                                  order in binary32; n = n partial sums per pixel */
+    uint32_t reserved[2];      /* must be 0 (VCRT_ERROR_INVALID_ARGUMENT otherwise) */
     uint32_t semantics;        /* VCRT_SEMANTICS_* */
 } VcrtRenderParams;
 
@@ -157,9 +158,13 @@ const char* cudaGetLastErrorString(void);
 int cudaGetDeviceImage(OUT void** devicePointer, OUT size_t* bytes);
 int cudaGetDeviceSums(OUT void** devicePointer, OUT size_t* bytes);
 
-/* ---- multi-GPU: samples-per-pixel sharded over ranks, one NCCL reduce of the float sums ---- */
+/* ---- multi-GPU: samples-per-pixel sharded over ranks, one NCCL reduce of the accumulation buffer ---- */
 /* One process per GPU: rank 0 calls cudaCommGetUniqueId, ships the 128 bytes to every rank by
-   any means (the Python host uses torch.distributed), every rank calls cudaCommInitRank. */
+   any means (the Python host uses torch.distributed), every rank calls cudaCommInitRank.
+   With a communicator, cudaRender is COLLECTIVE (unless VCRT_FLAG_NO_REDUCE): every rank must call it with the same image
+   size, depth, semantics and sampleChunks, and pass totalSamples when the shards are unequal.  Errors are not collective: a
+   rank whose call fails before the reduce (bad argument, out of memory) leaves the others waiting, as with any NCCL program -
+   validate on every rank before the first collective call.  A rank without samples passes samplesPerPixel = 0. */
 int cudaCommGetUniqueId(OUT void* id128);
 int cudaCommInitRank(IN const void* id128, IN int rank, IN int worldSize);
 int cudaCommDestroy(void);
@@ -172,6 +177,9 @@ int cudaCommBarrier(void);
    the denominator of the roofline (MEASURED_PEAKS.json carries HBM and bf16 only). */
 int cudaMeasureFp32Peak(OUT double* tflops, OUT double* smClockMHz);
 int cudaGetDeviceInfo(OUT int* smCount, OUT int* maxClockKHz, OUT char* name, IN size_t nameBytes);
+/* Evaluates the device code's schlick() (functions.glsl:58-62) on host arrays: the hook of the parity test that compares it
+   with the reference build on a dense set of inputs. */
+int cudaEvaluateSchlick(IN const float* cosine, IN const float* ior, IN uint32_t count, OUT float* reflectProb);
 /* CUDA events on the layer's own stream (the stream every kernel of cudaRender is launched on), so a caller
    can time a region of several calls on the device: record `slot` (0..15) now / milliseconds between two
    recorded slots (waits for the later one). */

@@ -47,6 +47,7 @@ void ref_world(float* out) {
 }
 float ref_rand(float x, float y) { return rand(vec2(x, y)); }
 float ref_schlick(float cosine, float ior) { return schlick(cosine, ior); }
+void ref_schlick_many(const float* cosine, const float* ior, int n, float* out) { for (int i = 0; i < n; i++) out[i] = schlick(cosine[i], ior[i]); }
 int ref_refract(const float* v, const float* n, float eta, float* out) {
     vec3 r; bool ok = modified_refract(vec3(v[0], v[1], v[2]), vec3(n[0], n[1], n[2]), eta, r);
     out[0] = r.x; out[1] = r.y; out[2] = r.z; return ok ? 1 : 0;

@@ -12,6 +12,9 @@ Files written:
   ref_hash_64x36_s4.npy      (36,64,4) f32 image rendered by the reference shader code, 4 spp, depth 50
   ref_hash_96x54_s2_d3.npy   (54,96,4) f32 the same at 2 spp, depth 3 (exercises bug B7: depth exhaustion)
   ref_kat.json               known answers: rand / schlick / refract / unit vector / first hits / image statistics
+  ref_hash_400x225_s256_u16.npz   (225,400,3) u16: the reference shader code at 400x225, 256 spp, depth 50, RGB quantised to
+                             2^-16 (error <= 7.7e-6, against an RMSE tolerance of 1e-2): the high-spp acceptance image
+  ref_schlick_dense.json     CRC-32 per block of 2^14 of ref_schlick over oracle_harness.schlick_inputs() (3 x 2^20 inputs)
 """
 import hashlib
 import json
@@ -84,6 +87,19 @@ def main():
     np.save(os.path.join(HERE, "ref_hash_400x225_s16_blocks8.npy"), blocks)
     with open(os.path.join(HERE, "ref_kat.json"), "w") as f:
         json.dump(kat, f, indent=1)
+    # the high-spp acceptance image (RMSE < 1e-2 wherever both sides have >= 128 spp)
+    hi, hst = ref.render(400, 225, 256, 50)
+    assert hi[..., :3].min() >= 0 and hi[..., :3].max() <= 1 and (hi[..., 3] == 1).all()
+    np.savez_compressed(os.path.join(HERE, "ref_hash_400x225_s256_u16.npz"),
+                        rgb=np.round(hi[..., :3].astype(np.float64) * 65535.0).astype(np.uint16),
+                        rays=np.uint64(hst["rays"]), exhausted=np.uint64(hst["exhausted"]),
+                        mean_rgb=hi[..., :3].reshape(-1, 3).astype(np.float64).mean(0))
+    # schlick on a dense input set: what functions.glsl:58-62 returns in the reference build (C powf of this image's libm)
+    cos, ior = oh.schlick_inputs()
+    out = ref.schlick_many(cos, ior)
+    with open(os.path.join(HERE, "ref_schlick_dense.json"), "w") as f:
+        json.dump({"inputs": "oracle_harness.schlick_inputs(1 << 20)", "count": int(out.size), "block": 1 << 14, "crc32": oh.block_crcs(out),
+                   "negative_results": int((out < 0).sum()), "nan_results": int(np.isnan(out).sum())}, f)
     print("golden written:", sorted(os.listdir(HERE)))
 
 

@@ -15,6 +15,27 @@ RNG_HASH, RNG_PHILOX = 0, 1
 CAMERA = np.array([13, 2, 3, 0, 0, 0, 0, 1, 0, 20], np.float32)   # globals.glsl:21-24
 
 
+def schlick_inputs(per_ior=1 << 20):
+    """The dense input set of the schlick parity test: per_ior cosines for each ior in (1.5, 2.4, 0.5).  Half of them are spread
+    over (-15, 2), a quarter lies in [0, 1] (1 - cosine is the positive base a refracting ray sees) and a quarter in (1, 15): the
+    cosine is an unnormalised dot product, so most calls of a render have a NEGATIVE base (bug B6).  Deterministic (PCG64 seed
+    20251105); used by make_golden.py and the tests alike."""
+    rng = np.random.default_rng(20251105)
+    cos, ior = [], []
+    for value in (1.5, 2.4, 0.5):
+        wide = rng.uniform(-15.0, 2.0, per_ior // 2).astype(np.float32)
+        unit = rng.uniform(0.0, 1.0, per_ior // 4).astype(np.float32)
+        above = rng.uniform(1.0, 15.0, per_ior - per_ior // 2 - per_ior // 4).astype(np.float32)
+        cos.append(np.concatenate([wide, unit, above])); ior.append(np.full(per_ior, value, np.float32))
+    return np.concatenate(cos), np.concatenate(ior)
+
+
+def block_crcs(values, block=1 << 14):
+    import zlib
+    raw = np.ascontiguousarray(values, np.float32)
+    return [zlib.crc32(raw[i:i + block].tobytes()) for i in range(0, raw.size, block)]
+
+
 def build_oracle():
     so = os.path.join(ORACLE_DIR, "_build", "liboracle.so")
     src = os.path.join(ORACLE_DIR, "vcrt_oracle.cpp")
@@ -114,6 +135,8 @@ class Reference:
         L.ref_rand.argtypes = [ctypes.c_float, ctypes.c_float]; L.ref_rand.restype = ctypes.c_float
         L.ref_schlick.argtypes = [ctypes.c_float, ctypes.c_float]; L.ref_schlick.restype = ctypes.c_float
         L.ref_refract.argtypes = [VP, VP, ctypes.c_float, VP]
+        if hasattr(L, "ref_schlick_many"):
+            L.ref_schlick_many.argtypes = [VP, VP, ctypes.c_int, VP]
         L.ref_unit_vector.argtypes = [VP, VP]
         L.ref_first_hit.argtypes = [VP, VP, VP]
         L.ref_world.argtypes = [VP]
@@ -129,6 +152,11 @@ class Reference:
         st = np.zeros(2, np.uint64)
         assert self.lib.ref_render(width, height, spp, depth, threads, img.ctypes.data_as(VP), st.ctypes.data_as(VP)) == 0
         return img, {"rays": int(st[0]), "exhausted": int(st[1])}
+
+    def schlick_many(self, cosine, ior):
+        cosine = np.ascontiguousarray(cosine, np.float32); ior = np.ascontiguousarray(ior, np.float32); out = np.empty_like(cosine)
+        self.lib.ref_schlick_many(cosine.ctypes.data_as(VP), ior.ctypes.data_as(VP), cosine.size, out.ctypes.data_as(VP))
+        return out
 
     def first_hit(self, origin, direction):
         o = np.ascontiguousarray(origin, np.float32); d = np.ascontiguousarray(direction, np.float32)

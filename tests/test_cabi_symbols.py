@@ -33,6 +33,30 @@ def test_every_declared_symbol_is_exported_and_bound(vcrt):
     assert sorted(cabi.PROTOTYPES) == names, "cabi.py bindings and the headers disagree"
 
 
+def prototypes(text):
+    """(return type, name, parameter list) of every function declared in a header, comments stripped."""
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    text = re.sub(r"//[^\n]*", "", text)
+    return [(r.strip(), n, " ".join(a.split())) for r, n, a in re.findall(r"^\s*([A-Za-z_][\w\s\*]*?)\b(\w+)\s*\(([^;{)]*)\)\s*;", text, flags=re.M)]
+
+
+def test_render_entry_matches_the_reference_header():
+    # The boundary claim checked against the reference TEXT where it is mounted: include/Renderer.hpp:14-20 declares
+    # BeginRenderingOperation / DrawNextFrame / EndRenderingOperation; the product header must declare the same three, same
+    # return type and parameter list, in the same order (it may add variables, not functions).
+    ref_header = os.path.join(os.environ.get("VCRT_REFERENCE", "/root/reference"), "include", "Renderer.hpp")
+    if not os.path.exists(ref_header):
+        pytest.skip("the reference tree is not mounted on this machine")
+    want = prototypes(open(ref_header).read())
+    got = prototypes(open(os.path.join(ROOT, "include", "Renderer.hpp")).read())
+    assert [n for _, n, _ in want] == ["BeginRenderingOperation", "DrawNextFrame", "EndRenderingOperation"]
+    assert got == want
+    # and main() calls them the way the reference's main does: Begin, the frame loop, End (VulkanComputeRayTracing.cpp:26-40)
+    main = open(os.path.join(ROOT, "vulkancomputeraytracing_b200", "host", "VulkanComputeRayTracing.cpp")).read()
+    order = [main.index(name + "(") for _, name, _ in want if name != "DrawNextFrame"]
+    assert order == sorted(order) and "PlatformEnterEventLoop" in main
+
+
 def test_struct_layouts():
     assert ctypes.sizeof(cabi.VcrtSphere) == 40          # structures.glsl:10-16, 10 floats
     assert ctypes.sizeof(cabi.VcrtCamera) == 40

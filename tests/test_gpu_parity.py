@@ -174,6 +174,14 @@ def test_call_order_errors(vcrt):
     assert vcrt.cudaDownloadImage(buf.ctypes.data_as(ctypes.c_void_p), 16) == cabi.VCRT_ERROR_INVALID_ARGUMENT
     p.width = 0
     assert vcrt.cudaRender(ctypes.byref(p)) == cabi.VCRT_ERROR_INVALID_ARGUMENT
+    p.width = 16; p.samplesPerPixel = 0                                              # 0 samples: only for a rank that joins a reduce
+    assert vcrt.cudaRender(ctypes.byref(p)) == cabi.VCRT_ERROR_INVALID_ARGUMENT
+    p.samplesPerPixel = 1
+    for slot in (0, 1):                                                              # reserved fields are reserved
+        p.reserved[slot] = 1
+        assert vcrt.cudaRender(ctypes.byref(p)) == cabi.VCRT_ERROR_INVALID_ARGUMENT
+        p.reserved[slot] = 0
+    assert vcrt.cudaRender(ctypes.byref(p)) == cabi.VCRT_SUCCESS
     host.destroy()
     assert vcrt.cudaDestroyRenderer() == cabi.VCRT_SUCCESS
 
@@ -286,8 +294,6 @@ def test_lbvh_widening_is_conservative_in_the_far_field(vcrt, case):
             simple, ss = host.render(480, 270, 2, depth=depth, traversal=SIMPLE, sample_chunks=1)
             tree, st = host.render(480, 270, 2, depth=depth, traversal=LBVH, sample_chunks=1)
             assert ss.rays == st.rays and np.array_equal(simple, tree)
-            nested, sn = host.render(480, 270, 2, depth=depth, traversal=LBVH, sample_chunks=1, shape=31)   # first generation: L = F, K = 64 eps
-            assert np.array_equal(nested, tree) and st.nodeVisits <= sn.nodeVisits
         assert ss.rays - 480 * 270 * 2 > 1000                     # enough hits for the comparison to mean something
     finally:
         host.destroy()
@@ -327,8 +333,6 @@ def test_lbvh_outlier_spheres_outside_the_tree(oracle, vcrt, case):
         cpu, cst = oracle.render(s, 120, 80, 2, depth=16, camera=host.camera_array(cam))
         gpu, st = host.render(120, 80, 2, depth=16, traversal=LBVH, sample_chunks=1)
         assert_same(gpu, st, cpu, cst)
-        nested, _ = host.render(120, 80, 2, depth=16, traversal=LBVH, sample_chunks=1, shape=31)
-        assert np.array_equal(nested, gpu)
     finally:
         host.destroy()
 
@@ -351,24 +355,22 @@ def test_lbvh_duplicates_and_coincident_centres(oracle, vcrt):
         host.destroy()
 
 
-@pytest.mark.parametrize("shape", [1, 10, 11, 20, 21])
-def test_every_brute_force_kernel_generation_agrees(oracle, vcrt, shape):
-    # development switch `shape`: 1 = first generation (LDS-fed filter), 10 / 11 = uniform-datapath scan (512x4 / 1024x2 rays),
-    # 20 / 21 = warp-compacted shading (1024x2 / 512x4 rays).  Same bits from all of them, in both semantics and accumulators.
-    for scene, cam in ((host.generate_scene(), None), (host.stress_scene(), None)):
-        host.upload_scene(scene, cam)
-        try:
-            cpu, cst = oracle.render(scene, 203, 113, 3, depth=9)
-            gpu, st = host.render(203, 113, 3, depth=9, traversal=BRUTE, sample_chunks=1, shape=shape)
-            assert_same(gpu, st, cpu, cst)
-            fixed, sf = host.render(203, 113, 3, depth=9, traversal=BRUTE, shape=shape)
-            assert sf.rays == cst["rays"] and np.abs(fixed - cpu).max() <= 2.0 ** -22
-            if shape != 1:
-                book, cb = oracle.render_book(scene, 96, 54, 2)
-                gb, sb = host.render(96, 54, 2, traversal=BRUTE, sample_chunks=1, shape=shape, semantics=cabi.VCRT_SEMANTICS_BOOK)
-                assert sb.rays == cb["rays"] and sb.depthExhausted == cb["exhausted"] and np.array_equal(gb, book)
-        finally:
-            host.destroy()
+@pytest.mark.parametrize("count", [650, 1100, 2200])
+def test_brute_force_kernel_ladder(oracle, vcrt, count):
+    # VCRT_TRAVERSAL_BRUTE picks its kernel by what fits shared memory beside the scene blob: render_scanu<1024,1> up to ~700
+    # spheres, render_scanu<512,2> up to ~1200, the first-generation render_scan<256,2> up to ~2400.  Same bits from all.
+    rng = np.random.default_rng(count)
+    scene = random_scene(rng, count, big=1)
+    host.upload_scene(scene)
+    try:
+        cpu, cst = oracle.render(scene, 120, 68, 2, depth=9)
+        gpu, st = host.render(120, 68, 2, depth=9, traversal=BRUTE, sample_chunks=1)
+        assert st.traversalUsed == BRUTE
+        assert_same(gpu, st, cpu, cst)
+        fixed, sf = host.render(120, 68, 2, depth=9, traversal=BRUTE)
+        assert sf.rays == cst["rays"] and np.abs(fixed - cpu).max() <= 2.0 ** -22
+    finally:
+        host.destroy()
 
 
 @pytest.mark.parametrize("traversal", [BRUTE, SIMPLE, LBVH])
@@ -383,27 +385,6 @@ def test_count_stats_match_oracle(oracle, gpu_scene, traversal):
     assert np.allclose(frac, [0.669, 0.199, 0.133], atol=0.02)              # SURVEY.md 3.4 probe
     plain, sp = host.render(160, 90, 4, traversal=traversal, sample_chunks=1)
     assert sum(sp.hitsByMaterial) == 0 and np.array_equal(plain, gpu)       # off by default, and never changes the image
-
-
-def test_both_lbvh_kernel_generations_agree(oracle, vcrt):
-    # development switch shape 31: the first-generation LBVH kernel (nested sample / bounce loops); the default is the flat
-    # loop whose idle lanes restart together.  Same bits as the oracle in strict order, same fixed-point image, both semantics.
-    for scene in (host.generate_scene(), host.stress_scene(), host.generate_scene(30)):
-        host.upload_scene(scene)
-        try:
-            for shape in (0, 31):
-                for depth in (9, 1, 0):
-                    cpu, cst = oracle.render(scene, 203, 113, 3, depth=depth)
-                    gpu, st = host.render(203, 113, 3, depth=depth, traversal=LBVH, sample_chunks=1, shape=shape)
-                    assert_same(gpu, st, cpu, cst)
-                book, cb = oracle.render_book(scene, 96, 54, 2)
-                gb, sb = host.render(96, 54, 2, traversal=LBVH, sample_chunks=1, shape=shape, semantics=cabi.VCRT_SEMANTICS_BOOK)
-                assert sb.rays == cb["rays"] and sb.depthExhausted == cb["exhausted"] and np.array_equal(gb, book)
-            nested, sn = host.render(203, 113, 5, traversal=LBVH, shape=31)
-            flat, sf = host.render(203, 113, 5, traversal=LBVH)
-            assert sf.rays == sn.rays and 0 < sf.nodeVisits <= sn.nodeVisits and np.array_equal(flat, nested)   # the flat kernel widens its boxes less
-        finally:
-            host.destroy()
 
 
 def test_acceptance_path_lengths_and_materials_vs_the_references_own_rng(oracle, gpu_scene):
@@ -448,6 +429,86 @@ def test_item_numbering_corner_cases(oracle, gpu_scene):
     for chunks in (2, 3, 7):                                              # float sums per chunk, chunks combined in order
         gpu, sg = host.render(96, 54, 7, traversal=LBVH, sample_chunks=chunks)
         assert sg.rays == cst["rays"] and np.abs(gpu - cpu).max() <= 2.0 ** -20
+
+
+@pytest.mark.parametrize("traversal", [BRUTE, LBVH])
+def test_chunk_counts_that_do_not_divide_the_samples(oracle, gpu_scene, traversal):
+    # 7 samples in 5 or 6 chunks are 4 runs of 2 (ceil(7 / ceil(7 / 5)) = 4), 9 samples in 4 chunks are 3 runs of 3: only the
+    # planes a kernel wrote may be summed.  A render with MORE planes goes first, so that a stale plane would show.
+    host.render(96, 54, 16, traversal=traversal, sample_chunks=16, download=False)
+    for spp, chunk_list in ((7, (5, 6, 4, 7)), (9, (4, 5, 8)), (5, (3, 4))):
+        cpu, cst = oracle.render(gpu_scene, 96, 54, spp)
+        for chunks in chunk_list:
+            gpu, sg = host.render(96, 54, spp, traversal=traversal, sample_chunks=chunks)
+            per_run = -(-spp // chunks)
+            assert sg.sampleChunksUsed == -(-spp // per_run) <= chunks
+            assert sg.rays == cst["rays"] and np.abs(gpu - cpu).max() <= 2.0 ** -20, (spp, chunks)
+            host.render(96, 54, 16, traversal=traversal, sample_chunks=16, download=False)
+
+
+def test_attenuation_outside_0_1_takes_float_sums(oracle, vcrt):
+    # The default accumulator (32.32 fixed point) needs radiance in [0, 1] per sample.  A scene with an albedo of 40 or a
+    # lambertian ratio of 3 (radiance far above 1, overflowing to inf after a few bounces) is summed in binary32 in sample order
+    # instead, whatever sampleChunks says: inf and NaN then propagate exactly as in the reference arithmetic.
+    scene = host.generate_scene(2)
+    scene[3, 4:7] = (40.0, 0.5, 2.0)
+    scene[5, 8] = 3.0 if int(scene[5, 7]) == 1 else scene[5, 8]
+    scene[0, 7] = 1.0; scene[0, 8] = 1e30; scene[0, 4:7] = 1.0      # a lambertian sphere that multiplies by 1e30 per hit
+    host.upload_scene(scene)
+    try:
+        cpu, cst = oracle.render(scene, 96, 54, 3, depth=12)
+        assert cpu[..., :3].max() > 1.5
+        for traversal in (BRUTE, LBVH):
+            for chunks in (0, 1):
+                gpu, st = host.render(96, 54, 3, depth=12, traversal=traversal, sample_chunks=chunks)
+                assert st.rays == cst["rays"] and np.array_equal(gpu, cpu, equal_nan=True), (traversal, chunks)
+    finally:
+        host.destroy()
+
+
+def test_uploading_the_same_scene_again_keeps_the_tree_and_the_bits(vcrt):
+    # cudaUploadScene with byte-identical spheres (a caller that uploads every frame) copies them again but keeps the LBVH;
+    # any change - one sphere, or just the order - rebuilds it.
+    scene = host.generate_scene(30)
+    host.upload_scene(scene)
+    try:
+        first, s1 = host.render(160, 90, 2, traversal=LBVH)
+        host.upload_scene(scene.copy())
+        again, s2 = host.render(160, 90, 2, traversal=LBVH)
+        assert np.array_equal(first, again) and s1.nodeVisits == s2.nodeVisits
+        moved = scene.copy(); moved[:-1, 1] += 0.07                # every sphere but the ground, 7 cm up
+        host.upload_scene(moved)
+        third, s3 = host.render(160, 90, 2, traversal=LBVH)
+        simple, s4 = host.render(160, 90, 2, traversal=SIMPLE)
+        assert s3.rays == s4.rays and np.abs(third - simple).max() <= 2.0 ** -22 and not np.array_equal(third, first)
+        cam = cabi.VcrtCamera((ctypes.c_float * 3)(-6, 3.5, 9), (ctypes.c_float * 3)(0.5, 0.4, -1), (ctypes.c_float * 3)(0.1, 1, 0), 35.0)
+        host.upload_scene(moved, cam)                                   # same spheres, another camera: tree kept, new view
+        other, s5 = host.render(160, 90, 2, traversal=LBVH)
+        simple, s6 = host.render(160, 90, 2, traversal=SIMPLE)
+        assert s5.rays == s6.rays and np.abs(other - simple).max() <= 2.0 ** -22
+    finally:
+        host.destroy()
+
+
+def test_schlick_dense(vcrt):
+    # functions.glsl:58-62 on 3 x 2^20 inputs: the device routine (pow(x, 5.) restated from glibc's powf, csrc/vcrt_powf.cuh)
+    # against what the reference build returned (golden from oracle/_ref; live too where that build travelled to this machine).
+    # Bar: 0 mismatches.
+    with open(os.path.join(GOLDEN, "ref_schlick_dense.json")) as f:
+        want = json.load(f)
+    cos, ior = oh.schlick_inputs()
+    out = np.empty_like(cos)
+    cabi.check(vcrt.cudaEvaluateSchlick(cos.ctypes.data, ior.ctypes.data, cos.size, out.ctypes.data))
+    host.destroy()
+    got = oh.block_crcs(out, want["block"])
+    differing = sum(a != b for a, b in zip(got, want["crc32"]))
+    ref = oh.Reference.open()
+    mismatches = None
+    if ref is not None:
+        live = ref.schlick_many(cos, ior)
+        mismatches = int((out.view(np.uint32) != live.view(np.uint32)).sum())
+    print(f"schlick: {cos.size} inputs, {differing} of {len(got)} golden blocks differ, live mismatches: {mismatches}")
+    assert differing == 0 and not mismatches
 
 
 @pytest.mark.parametrize("case", ["zero_and_negative_radius", "tiny_and_huge", "nan_and_inf_spheres", "degenerate_camera", "coincident_centres",

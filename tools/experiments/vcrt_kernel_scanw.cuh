@@ -19,7 +19,7 @@
     same; tests/test_gpu_parity.py holds the kernel bit-identical to the oracle like the others.
 */
 #pragma once
-#include "vcrt_kernel_scanu.cuh"
+#include "../../vulkancomputeraytracing_b200/csrc/vcrt_kernel_scanu.cuh"
 
 namespace vcrt {
 
@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanw_kernel(const unsigned
                 const int nScan = exhaustive ? scanCount : (int)listCount, nAll = nScan + (count - scanCount);
                 for (int e = 0; e < nAll; e++) {
                     const int j = e >= nScan ? scanCount + (e - nScan) : (exhaustive ? e : (int)TLIST(e));
-                    hit_exact(sShape[j], j, ray, a, rec);
+                    hit_exact(sShape[j], j, ray, a, rec, !((exhaustMask >> r) & 1u));
                 }
                 WS(WF_HITT, r, tid) = __float_as_uint(rec.t);
                 WS(WF_HITI, r, tid) = (uint32_t)rec.index;
@@ -294,10 +294,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanw_kernel(const unsigned
                 uint32_t s = WS(WF_SAMPLE, r, t);
                 const uint32_t s1 = WS(WF_END, r, t);
                 if (FIXED) {
-                    long long* acc = args.fixedSums + 4 * (size_t)pixel;
-                    if (result.x != 0.f) atomicAdd((unsigned long long*)acc + 0, (unsigned long long)__float2ll_rn(result.x * kFixedOne));
-                    if (result.y != 0.f) atomicAdd((unsigned long long*)acc + 1, (unsigned long long)__float2ll_rn(result.y * kFixedOne));
-                    if (result.z != 0.f) atomicAdd((unsigned long long*)acc + 2, (unsigned long long)__float2ll_rn(result.z * kFixedOne));
+                    add_fixed(args.fixedSums, pixel, result);
                     s++;
                 } else {
                     const uint32_t chunk = (s1 - 1u) / sppPerChunk, s0 = chunk * sppPerChunk;

@@ -88,6 +88,7 @@ PROTOTYPES = {
     "cudaCommBarrier": (ctypes.c_int, []),
     "cudaMeasureFp32Peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
     "cudaGetDeviceInfo": (ctypes.c_int, [ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), ctypes.c_char_p, ctypes.c_size_t]),
+    "cudaEvaluateSchlick": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p]),
     "cudaStreamMark": (ctypes.c_int, [ctypes.c_uint32]),
     "cudaStreamElapsed": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(ctypes.c_float)]),
     "cudaFlushL2": (ctypes.c_int, []),

@@ -11,7 +11,10 @@
 #include "vcrt_kernel_scan.cuh"
 #include "vcrt_kernel_lbvh.cuh"
 #include "vcrt_kernel_scanu.cuh"
-#include "vcrt_kernel_scanw.cuh"
+#ifdef VCRT_EXPERIMENTS   // A/B kernels that no default call reaches: tools/experiments/README.md (build with VCRT_EXTRA_NVCC=-DVCRT_EXPERIMENTS)
+#include "../../tools/experiments/vcrt_kernel_scanw.cuh"
+#include "../../tools/experiments/vcrt_kernel_lbvh_gen1.cuh"
+#endif
 
 #include <cub/device/device_radix_sort.cuh>
 
@@ -40,6 +43,10 @@ static SceneBlob cudaComputeSceneHeader;
 static bool cudaComputeSceneReady = false;
 static bool cudaComputeSceneInConstant = false;   // the filter table of the uniform-datapath scan is loaded
 static bool cudaComputeSceneNonFinite = false;    // a centre or radius is NaN / inf / beyond the tame range (vcrt_device.cuh): only the in-order scan reproduces the reference
+static bool cudaComputeSceneBounded = true;       // every attenuation is in [0, 1]: a sample's radiance is, too, and the 32.32 fixed-point sums cannot overflow
+static unsigned char* cudaComputeHostBlob = nullptr;   // host copy of the last uploaded blob: an identical upload keeps the LBVH
+static size_t cudaComputeHostBlobBytes = 0;
+static size_t cudaComputeSceneBlobCapacity = 0;
 struct SceneExtent { float centreMin[3], centreMax[3], radiusMin, radiusMax; };
 // LBVH over the scan spheres (device indices [0, scanCount)), built on first use after an upload
 static bool cudaComputeBvhReady = false;
@@ -53,7 +60,7 @@ static float4* cudaComputeSumPlanes = nullptr;          // [chunks][W*H] partial
 static size_t cudaComputeSumPlanesBytes = 0;
 static float4* cudaComputeAccumulated = nullptr;        // [W*H] sums over all samples so far (this device)
 static float4* cudaComputeReduced = nullptr;            // [W*H] sums after the cross-device reduce
-static long long* cudaComputeFixedSums = nullptr;       // [W*H][4] signed 32.32 fixed-point sums (order-independent accumulation)
+static long long* cudaComputeFixedSums = nullptr;       // [W*H][kFixedLanes] signed 32.32 fixed-point sums (order-independent accumulation)
 static long long* cudaComputeFixedReduced = nullptr;    // the same after the cross-device reduce
 static bool cudaComputeAccumulatedIsFixed = false;
 static float4* cudaComputeResultImage = nullptr;        // [W*H] normalised RGBA32F (reference Renderer.cpp:433-453)
@@ -77,8 +84,11 @@ static int fail(int code, const char* fmt, const char* detail) {
                         #expr ": %s", cudaGetErrorString(cudaTryResult));                 \
     } while (0)
 
+// Every entry point comes through here first: the layer's device is made current on EVERY call, because a host that shares
+// the process with torch or another CUDA user (or calls from another thread) may have switched devices in between, and
+// allocations, launches and the __constant__ table are all per device.
 static int ensureDevice(void) {
-    if (cudaComputeDeviceReady) return VCRT_SUCCESS;
+    if (cudaComputeDeviceReady) { CUDA_TRY(cudaSetDevice(cudaComputeDevice)); return VCRT_SUCCESS; }
     int deviceCount = 0;
     cudaError_t e = cudaGetDeviceCount(&deviceCount);
     if (e != cudaSuccess || deviceCount == 0)
@@ -185,9 +195,15 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
     float4* surf = (float4*)(host + hdr.offSurf); int* kind = (int*)(host + hdr.offKind);
     uint32_t* orig = (uint32_t*)(host + hdr.offOrig);
     cudaComputeSceneNonFinite = false;
+    cudaComputeSceneBounded = true;
     for (uint32_t j = 0; j < count; j++) {
         const VcrtSphere& s = spheres[order[j]];
         orig[j] = order[j];
+        // attenuation per hit: lambertian albedo * texture.y (textures.glsl:22), metal albedo (:60), glass 1; all in [0, 1] keeps
+        // the radiance of a sample in [0, 1] (the sky of functions.glsl:89 is), which is what the fixed-point sums rely on
+        const float ratio = (int)s.texture[0] == 1 ? s.texture[1] : 1.0f;
+        if (!(s.colour[0] >= 0.f && s.colour[0] <= 1.f && s.colour[1] >= 0.f && s.colour[1] <= 1.f && s.colour[2] >= 0.f && s.colour[2] <= 1.f && ratio >= 0.f && ratio <= 1.f))
+            cudaComputeSceneBounded = false;
         // (negated comparisons: a NaN lands here too)
         if (!(fabsf(s.center[0]) <= kTameSceneMax && fabsf(s.center[1]) <= kTameSceneMax && fabsf(s.center[2]) <= kTameSceneMax && fabsf(s.radius) <= kTameSceneMax))
             cudaComputeSceneNonFinite = true;
@@ -230,15 +246,24 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
     cudaComputeHostShape = new float4[count ? count : 1];
     memcpy(cudaComputeHostShape, shape, sizeof(float4) * count);
 
-    if (cudaComputeSceneBlob) { cudaFree(cudaComputeSceneBlob); cudaComputeSceneBlob = nullptr; }
+    // The same bytes as last time (a caller that uploads every frame, bench.py's e2e leg): the copy below still happens - the
+    // caller's data is what gets rendered - but the tree built from those bytes stays (8 ms at 100 k spheres).
+    const bool sameScene = cudaComputeSceneReady && cudaComputeHostBlob && cudaComputeHostBlobBytes == hdr.bytes && memcmp(cudaComputeHostBlob, host, hdr.bytes) == 0;
     cudaComputeSceneReady = false;
-    cudaError_t e = cudaMalloc(&cudaComputeSceneBlob, hdr.bytes);
+    cudaError_t e = cudaSuccess;
+    if (hdr.bytes > cudaComputeSceneBlobCapacity) {   // the device blob keeps its address while it fits (the tree points into it)
+        if (cudaComputeSceneBlob) { cudaFree(cudaComputeSceneBlob); cudaComputeSceneBlob = nullptr; }
+        cudaComputeSceneBlobCapacity = 0; cudaComputeBvhReady = false;
+        e = cudaMalloc(&cudaComputeSceneBlob, hdr.bytes);
+        if (e == cudaSuccess) cudaComputeSceneBlobCapacity = hdr.bytes;
+    }
     if (e == cudaSuccess) e = cudaMemcpyAsync(cudaComputeSceneBlob, host, hdr.bytes, cudaMemcpyHostToDevice, cudaComputeStream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(cudaComputeStream);
-    free(host);
-    if (e != cudaSuccess) return fail(VCRT_ERROR_CUDA, "scene upload: %s", cudaGetErrorString(e));
+    if (e != cudaSuccess) { free(host); cudaComputeBvhReady = false; return fail(e == cudaErrorMemoryAllocation ? VCRT_ERROR_OUT_OF_MEMORY : VCRT_ERROR_CUDA, "scene upload: %s", cudaGetErrorString(e)); }
+    if (cudaComputeHostBlob) free(cudaComputeHostBlob);
+    cudaComputeHostBlob = host; cudaComputeHostBlobBytes = hdr.bytes;   // kept for the comparison above
     cudaComputeSceneHeader = hdr;
-    cudaComputeBvhReady = false;
+    if (!sameScene) cudaComputeBvhReady = false;
     cudaComputeCamera = *camera;
     cudaComputeSceneReady = true;
     cudaComputeImageValid = false;
@@ -304,63 +329,78 @@ __global__ void normalise_kernel(float4* image, const float4* sums, uint32_t pix
 __global__ void fixed_to_float_kernel(float4* sums, const long long* fixedSums, uint32_t pixels) {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= pixels) return;
-    const long long* f = fixedSums + 4 * (size_t)p;
+    const long long* f = fixedSums + kFixedLanes * (size_t)p;
     const double s = 1.0 / 4294967296.0;
     sums[p] = make_float4((float)((double)f[0] * s), (float)((double)f[1] * s), (float)((double)f[2] * s), 0.f);
 }
 __global__ void normalise_fixed_kernel(float4* image, const long long* fixedSums, uint32_t pixels, double samples, int gamma) {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= pixels) return;
-    const long long* f = fixedSums + 4 * (size_t)p;
+    const long long* f = fixedSums + kFixedLanes * (size_t)p;
     const double s = 1.0 / (4294967296.0 * samples);
     image[p] = make_float4(to_gamma((float)((double)f[0] * s), gamma), to_gamma((float)((double)f[1] * s), gamma), to_gamma((float)((double)f[2] * s), gamma), 1.0f);
 }
-// FFMA-only kernel: the measured FP32 roofline denominator.
-__global__ void fp32_peak_kernel(float* out, int iters, float a, float b, long long* cycles) {
+// FFMA-only kernel: what the FP32 pipe of this GPU sustains when nothing else is asked of it.  512 FFMAs per trip (8
+// independent chains x 64) against 3 loop instructions, so the loop overhead is below 0.6 % (round 1 had 64 per trip and read
+// 4.5 % low).  bench.py reports it beside the nominal peak SMs x 128 lanes x 2 x sampled SM clock, which is the denominator.
+__global__ void fp32_peak_kernel(float* out, int iters, float a, float b) {
     float x[8];
 #pragma unroll
     for (int c = 0; c < 8; c++) x[c] = threadIdx.x * 1e-3f + c;
-    long long t0 = clock64();
 #pragma unroll 1
     for (int i = 0; i < iters; i++) {
 #pragma unroll
-        for (int u = 0; u < 8; u++)
+        for (int u = 0; u < 64; u++)
 #pragma unroll
             for (int c = 0; c < 8; c++) x[c] = fmaf(x[c], a, b);
     }
-    long long t1 = clock64();
     float s = 0;
 #pragma unroll
     for (int c = 0; c < 8; c++) s += x[c];
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
-    if (threadIdx.x == 0 && blockIdx.x == 0) *cycles = t1 - t0;
 }
 
 extern "C" int cudaMeasureFp32Peak(OUT double* tflops, OUT double* smClockMHz) {
     int rc = ensureDevice();
     if (rc) return rc;
-    const int threads = 512, blocks = cudaComputeSmCount * 4, iters = 8192;
-    float* out = nullptr; long long* cycles = nullptr;
+    const int threads = 512, blocks = cudaComputeSmCount * 4, iters = 2048;
+    float* out = nullptr;
     CUDA_TRY(cudaMalloc(&out, sizeof(float) * threads * blocks));
-    CUDA_TRY(cudaMalloc(&cycles, sizeof(long long)));
     float best = 1e30f;
-    for (int rep = 0; rep < 6; rep++) {
+    for (int rep = 0; rep < 8; rep++) {   // ~5 ms each; the first ones bring the clock up
         CUDA_TRY(cudaEventRecord(cudaComputeEvents[2], cudaComputeStream));
-        fp32_peak_kernel<<<blocks, threads, 0, cudaComputeStream>>>(out, iters, 1.0001f, 1e-4f, cycles);
+        fp32_peak_kernel<<<blocks, threads, 0, cudaComputeStream>>>(out, iters, 1.0001f, 1e-4f);
         CUDA_TRY(cudaEventRecord(cudaComputeEvents[3], cudaComputeStream));
         CUDA_TRY(cudaEventSynchronize(cudaComputeEvents[3]));
         float ms = 0; CUDA_TRY(cudaEventElapsedTime(&ms, cudaComputeEvents[2], cudaComputeEvents[3]));
-        if (rep > 0 && ms < best) best = ms;
+        if (rep > 1 && ms < best) best = ms;
     }
-    long long hostCycles = 0;
-    CUDA_TRY(cudaMemcpy(&hostCycles, cycles, sizeof hostCycles, cudaMemcpyDeviceToHost));
-    cudaFree(out); cudaFree(cycles);
-    double flop = (double)threads * blocks * iters * 64.0 * 2.0;
+    cudaFree(out);
+    const double flop = (double)threads * blocks * iters * 512.0 * 2.0;
     if (tflops) *tflops = flop / (best * 1e-3) * 1e-12;
-    // one block's loop = 4 resident blocks/SM x 16 warps sharing 4 schedulers: cycles are wall cycles of that SM
-    (void)hostCycles;
     // the SM clock this rate corresponds to if every FP32 lane retired one FMA per cycle (128 lanes per SM)
-    if (smClockMHz && tflops) *smClockMHz = *tflops * 1e12 / (2.0 * 128.0 * cudaComputeSmCount) * 1e-6;
+    if (smClockMHz) *smClockMHz = flop / (best * 1e-3) / (2.0 * 128.0 * cudaComputeSmCount) * 1e-6;
+    return VCRT_SUCCESS;
+}
+
+// schlick() of the device code on a host array (tests/test_gpu_parity.py compares it with the reference build's ref_schlick).
+__global__ void schlick_kernel(const float* cosine, const float* ior, uint32_t count, float* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) out[i] = schlick(cosine[i], ior[i]);
+}
+extern "C" int cudaEvaluateSchlick(IN const float* cosine, IN const float* ior, IN uint32_t count, OUT float* reflectProb) {
+    if ((!cosine || !ior || !reflectProb) && count) return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaEvaluateSchlick: null argument%s", "");
+    int rc = ensureDevice(); if (rc) return rc;
+    if (!count) return VCRT_SUCCESS;
+    float* dev = nullptr;
+    CUDA_TRY(cudaMalloc(&dev, sizeof(float) * 3 * (size_t)count));
+    cudaError_t e = cudaMemcpyAsync(dev, cosine, sizeof(float) * count, cudaMemcpyHostToDevice, cudaComputeStream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dev + count, ior, sizeof(float) * count, cudaMemcpyHostToDevice, cudaComputeStream);
+    if (e == cudaSuccess) { schlick_kernel<<<(count + 255u) / 256u, 256, 0, cudaComputeStream>>>(dev, dev + count, count, dev + 2 * (size_t)count); e = cudaGetLastError(); }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(reflectProb, dev + 2 * (size_t)count, sizeof(float) * count, cudaMemcpyDeviceToHost, cudaComputeStream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(cudaComputeStream);
+    cudaFree(dev);
+    if (e != cudaSuccess) return fail(VCRT_ERROR_CUDA, "cudaEvaluateSchlick: %s", cudaGetErrorString(e));
     return VCRT_SUCCESS;
 }
 
@@ -406,8 +446,8 @@ static int ensureImageBuffers(uint32_t width, uint32_t height, uint32_t chunks) 
         CUDA_TRY(cudaMalloc(&cudaComputeAccumulated, pixels * sizeof(float4)));
         CUDA_TRY(cudaMalloc(&cudaComputeReduced, pixels * sizeof(float4)));
         CUDA_TRY(cudaMalloc(&cudaComputeResultImage, pixels * sizeof(float4)));
-        CUDA_TRY(cudaMalloc(&cudaComputeFixedSums, pixels * 4 * sizeof(long long)));
-        CUDA_TRY(cudaMalloc(&cudaComputeFixedReduced, pixels * 4 * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&cudaComputeFixedSums, pixels * kFixedLanes * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&cudaComputeFixedReduced, pixels * kFixedLanes * sizeof(long long)));
         cudaComputeImageWidth = width; cudaComputeImageHeight = height;
     }
     const size_t need = pixels * sizeof(float4) * chunks;
@@ -596,7 +636,12 @@ static int ensureBvh(void) {
 
 template <bool FIXED, bool STATS, bool FLAT>
 static int launchLbvh(const RenderArgs& args, uint32_t* launches) {
+#ifdef VCRT_EXPERIMENTS
     auto kernel = FLAT ? render_lbvh_flat_kernel<FIXED, STATS> : render_lbvh_kernel<FIXED, STATS>;
+#else
+    static_assert(FLAT, "the first-generation LBVH kernel is an experiment (tools/experiments)");
+    auto kernel = render_lbvh_flat_kernel<FIXED, STATS>;
+#endif
     int perSm = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, 256, 0));
     if (perSm < 1) perSm = 1;
@@ -638,6 +683,7 @@ static int launchScanU(const RenderArgs& args, uint32_t* launches) {
     *launches += 1;
     return VCRT_SUCCESS;
 }
+#ifdef VCRT_EXPERIMENTS
 template <int THREADS, int PAIRS, int LCAP, bool FIXED>
 static int launchScanW(const RenderArgs& args, uint32_t* launches) {
     using Cfg = ScanWConfig<THREADS, PAIRS, LCAP>;
@@ -656,6 +702,7 @@ static bool scanWFits(int threads, int pairs, int lcap) {
     size_t state = (size_t)WF_COUNT * 2 * pairs * threads * 4, lists = (size_t)lcap * threads * 2, map = (size_t)2 * pairs * threads;
     return cudaComputeSceneInConstant && 16 + (size_t)cudaComputeSceneHeader.bytes + state + lists + map <= 227 * 1024;
 }
+#endif
 static bool scanUFits(int threads, int pairs, int lcap) {
     size_t state = (size_t)SF_COUNT * 2 * pairs * threads * 4, lists = (size_t)lcap * threads * 2;
     return cudaComputeSceneInConstant && 16 + (size_t)cudaComputeSceneHeader.bytes + state + lists <= 227 * 1024;
@@ -670,8 +717,14 @@ static bool scanFits(int threads, int pairs, int cap) {
 
 extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     if (!p) return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRender: null params%s", "");
-    if (!p->width || !p->height || !p->samplesPerPixel || p->width > 65535u || p->height > 65535u || p->samplesPerPixel >= (1u << 24))
-        return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRender: width/height must be 1..65535 and samplesPerPixel 1..2^24-1%s", "");
+    // A rank of a multi-GPU job may have no sample of its own (total spp below the rank count: the reference's default is 1 spp,
+    // globals.glsl:12).  It still has to join the reduce, or the other ranks wait for ever: 0 samples is valid there.
+    const bool joinsReduce = cudaComputeComm && cudaComputeWorldSize > 1 && !(p->flags & VCRT_FLAG_NO_REDUCE);
+    if (!p->width || !p->height || (!p->samplesPerPixel && !joinsReduce) || p->width > 65535u || p->height > 65535u || p->samplesPerPixel >= (1u << 24))
+        return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRender: width/height must be 1..65535 and samplesPerPixel 1..2^24-1 (0 only for a rank that just joins the reduce)%s", "");
+#ifndef VCRT_EXPERIMENTS
+    if (p->reserved[0] || p->reserved[1]) return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRender: reserved fields must be 0%s", "");
+#endif
     int rc = ensureDevice(); if (rc) return rc;
     if (!cudaComputeSceneReady) return fail(VCRT_ERROR_NOT_READY, "cudaRender before cudaUploadScene%s", "");
 
@@ -688,7 +741,9 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         return fail(VCRT_ERROR_UNSUPPORTED, "scene does not fit shared memory for VCRT_TRAVERSAL_BRUTE%s", "");
     if (traversal > VCRT_TRAVERSAL_SIMPLE) return fail(VCRT_ERROR_INVALID_ARGUMENT, "unknown traversal%s", "");
 
+#ifdef VCRT_EXPERIMENTS
     const bool wide = scanFits(512, 2, 12);
+#endif
     const uint32_t pixels = p->width * p->height;
     // Accumulation mode.  sampleChunks == 0 (default, brute force only): 32.32 fixed-point sums, every sample added
     // with an integer RED, work items of a few samples each -> good load balance and bits that do not depend on the
@@ -697,28 +752,26 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     bool fixedMode = false;
     if (traversal == VCRT_TRAVERSAL_BRUTE || traversal == VCRT_TRAVERSAL_LBVH) {
         chunks = p->sampleChunks;
-        fixedMode = chunks == 0;
+        // the fixed-point accumulator needs radiance in [0, 1] per sample; a scene with an attenuation outside [0, 1] (or NaN)
+        // gets float sums in strict sample order instead, where inf / NaN propagate as they do in the reference
+        fixedMode = chunks == 0 && cudaComputeSceneBounded;
         if (chunks > p->samplesPerPixel) chunks = p->samplesPerPixel;
         if (chunks < 1u) chunks = 1u;
     }
     if (traversal == VCRT_TRAVERSAL_LBVH) { rc = ensureBvh(); if (rc) return rc; }
-    // Work items.  Fixed-point mode: 1 sample per item is fastest (measured; it keeps the lanes of a warp on neighbouring
-    // pixels); more only where the 32-bit item numbering needs it (4K x 520 spp on one GPU is already 2^32 pixel-samples).
-    // Strict modes: one item per pixel and chunk.
-    ItemPlan plan; memset(&plan, 0, sizeof plan);
-    {
-        const uint64_t tiles = (uint64_t)((p->width + 7u) / 8u) * ((p->height + 3u) / 4u);
-        if (tiles * 32u >= (1ull << 31)) return fail(VCRT_ERROR_INVALID_ARGUMENT, "image too large%s", "");
-        plan.tilesX = (p->width + 7u) / 8u; plan.pixelsPadded = (uint32_t)(tiles * 32u);
-        uint32_t perRun = fixedMode ? (p->reserved[0] ? p->reserved[0] : 1u) : (p->samplesPerPixel + chunks - 1u) / chunks;
-        const uint64_t kMaxItems = (1ull << 32) - (1ull << 24);
-        const uint64_t need = ((uint64_t)plan.pixelsPadded * p->samplesPerPixel + kMaxItems - 1) / kMaxItems;
-        if (fixedMode && need > perRun) perRun = (uint32_t)need;
-        if (fixedMode && p->samplesPerPixel / perRun >= (1u << 21)) perRun = p->samplesPerPixel >> 21;   // keeps runsPerPixel < 2^22
+    // Work items.  Fixed-point mode: 1 sample per item (measured fastest: it keeps the lanes of a warp on neighbouring pixels;
+    // 2 per item cost the brute-force kernel 6 % and the LBVH kernel 20 %), and where the 32-bit item numbering cannot hold
+    // pixels x samples (4K x 520 spp is already 2^32) the call is split into several launches over sample sub-ranges - the
+    // integer sums do not care.  Strict modes: one item per pixel and chunk, one launch.
+    const uint64_t tilesAll = (uint64_t)((p->width + 7u) / 8u) * ((p->height + 3u) / 4u);
+    if (tilesAll * 32u >= (1ull << 31)) return fail(VCRT_ERROR_INVALID_ARGUMENT, "image too large%s", "");
+    const uint64_t kMaxItems = (1ull << 32) - (1ull << 24);
+    auto planFor = [&](uint32_t spp, uint32_t perRun, ItemPlan& plan) -> bool {
+        memset(&plan, 0, sizeof plan);
+        plan.tilesX = (p->width + 7u) / 8u; plan.pixelsPadded = (uint32_t)(tilesAll * 32u);
         if (perRun < 1u) perRun = 1u;
-        plan.sppPerRun = perRun; plan.runsPerPixel = (p->samplesPerPixel + perRun - 1u) / perRun;
-        if ((uint64_t)plan.pixelsPadded * plan.runsPerPixel > kMaxItems || plan.runsPerPixel >= (1u << 22))
-            return fail(VCRT_ERROR_INVALID_ARGUMENT, "too many work items: lower sampleChunks / samplesPerPixel per call%s", "");
+        plan.sppPerRun = perRun; plan.runsPerPixel = (spp + perRun - 1u) / perRun;
+        if ((uint64_t)plan.pixelsPadded * plan.runsPerPixel > kMaxItems || plan.runsPerPixel >= (1u << 22)) return false;
         plan.totalItems = plan.pixelsPadded * plan.runsPerPixel;
         const uint32_t fullBands = plan.pixelsPadded >> VCRT_BAND_SHIFT;
         plan.fullBandRuns = fullBands * plan.runsPerPixel;
@@ -734,8 +787,28 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
             while (stride > 1u && gcd(stride, plan.tiles) != 1u) stride--;
             plan.tileStride = stride;
         }
+        return true;
+    };
+    uint32_t passes = 1u, perRunFixed = 1u;
+    if (fixedMode) {
+#ifdef VCRT_EXPERIMENTS
+        if (p->reserved[0]) perRunFixed = p->reserved[0];
+#endif
+        const uint64_t items = tilesAll * 32u * ((p->samplesPerPixel + perRunFixed - 1u) / perRunFixed);
+        passes = (uint32_t)((items + kMaxItems - 1) / kMaxItems);
+        const uint32_t byRuns = (p->samplesPerPixel / perRunFixed) / ((1u << 22) - 2u) + 1u;   // runs per pixel and launch stay below 2^22
+        if (passes < byRuns) passes = byRuns;
+        if (passes < 1u) passes = 1u;
     }
-    rc = ensureImageBuffers(p->width, p->height, chunks); if (rc) return rc;
+    ItemPlan plan;
+    if (!planFor(fixedMode ? (p->samplesPerPixel + passes - 1u) / passes : p->samplesPerPixel,
+                 fixedMode ? perRunFixed : (p->samplesPerPixel + chunks - 1u) / chunks, plan))
+        return fail(VCRT_ERROR_INVALID_ARGUMENT, "too many work items: lower sampleChunks / samplesPerPixel per call%s", "");
+    // Float modes: the kernels write one plane per run, and ceil(spp / ceil(spp / chunks)) can be smaller than the chunk count
+    // asked for (7 samples in 5 chunks = 4 runs of 2): only the planes that are written may be summed.
+    if (!fixedMode) chunks = plan.runsPerPixel;
+    const bool traces = p->maxDepth != 0 && p->samplesPerPixel != 0;   // otherwise no kernel runs and the sums of this call are zero
+    rc = ensureImageBuffers(p->width, p->height, chunks ? chunks : 1u); if (rc) return rc;
     const bool keep = (p->flags & VCRT_FLAG_ACCUMULATE) && cudaComputeAccumulatedSamples > 0;
     if (keep && fixedMode != cudaComputeAccumulatedIsFixed)
         return fail(VCRT_ERROR_UNSUPPORTED, "VCRT_FLAG_ACCUMULATE across different accumulation modes%s", "");
@@ -755,8 +828,8 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     CUDA_TRY(cudaEventRecord(cudaComputeEvents[0], cudaComputeStream));
     CUDA_TRY(cudaMemsetAsync(cudaComputeCounters, 0, sizeof(unsigned long long) * CTR_COUNT, cudaComputeStream));
     CUDA_TRY(cudaEventRecord(cudaComputeEvents[1], cudaComputeStream));
-    if (fixedMode && !keep) CUDA_TRY(cudaMemsetAsync(cudaComputeFixedSums, 0, (size_t)pixels * 4 * sizeof(long long), cudaComputeStream));
-    if (p->maxDepth == 0) {   // no pass of functions.glsl:73 runs: every sample is black (bug B7)
+    if (fixedMode && !keep) CUDA_TRY(cudaMemsetAsync(cudaComputeFixedSums, 0, (size_t)pixels * kFixedLanes * sizeof(long long), cudaComputeStream));
+    if (!traces) {   // depth 0: no pass of functions.glsl:73 runs, every sample is black (bug B7); 0 samples: nothing to add
         CUDA_TRY(cudaMemsetAsync(cudaComputeSumPlanes, 0, (size_t)pixels * sizeof(float4) * chunks, cudaComputeStream));
     } else if (traversal == VCRT_TRAVERSAL_SIMPLE) {
         DeviceScene scene; memset(&scene, 0, sizeof scene);
@@ -768,38 +841,59 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         render_simple_kernel<<<grid, 128, 0, cudaComputeStream>>>(scene, args);
         CUDA_TRY(cudaGetLastError());
         launches++;
-    } else if (traversal == VCRT_TRAVERSAL_LBVH) {
-        const bool flat = p->reserved[1] != 31;   // experiment switch: 31 = the first-generation nested-loop kernel
+    } else for (uint32_t pass = 0, done = 0; pass < passes; pass++) {
+        // one launch per sample sub-range (more than one only in fixed-point mode, see the work-item plan above)
+        const uint32_t passSpp = p->samplesPerPixel / passes + (pass < p->samplesPerPixel % passes ? 1u : 0u);
+        if (!passSpp) continue;
+        if (passes > 1u) {
+            args.spp = passSpp; args.sampleOffset = p->sampleOffset + done;
+            if (!planFor(passSpp, perRunFixed, args.plan)) return fail(VCRT_ERROR_INVALID_ARGUMENT, "too many work items%s", "");
+        }
+        done += passSpp;
+      if (traversal == VCRT_TRAVERSAL_LBVH) {
         const bool stats = (args.flags & kFlagCountStats) != 0;
-        if (flat) rc = stats ? (fixedMode ? launchLbvh<true, true, true>(args, &launches) : launchLbvh<false, true, true>(args, &launches))
-                             : (fixedMode ? launchLbvh<true, false, true>(args, &launches) : launchLbvh<false, false, true>(args, &launches));
-        else rc = stats ? (fixedMode ? launchLbvh<true, true, false>(args, &launches) : launchLbvh<false, true, false>(args, &launches))
-                        : (fixedMode ? launchLbvh<true, false, false>(args, &launches) : launchLbvh<false, false, false>(args, &launches));
+#ifdef VCRT_EXPERIMENTS
+        if (p->reserved[1] == 31)   // the first-generation nested-loop kernel
+            rc = stats ? (fixedMode ? launchLbvh<true, true, false>(args, &launches) : launchLbvh<false, true, false>(args, &launches))
+                       : (fixedMode ? launchLbvh<true, false, false>(args, &launches) : launchLbvh<false, false, false>(args, &launches));
+        else
+#endif
+        rc = stats ? (fixedMode ? launchLbvh<true, true, true>(args, &launches) : launchLbvh<false, true, true>(args, &launches))
+                   : (fixedMode ? launchLbvh<true, false, true>(args, &launches) : launchLbvh<false, false, true>(args, &launches));
         if (rc) return rc;
-    } else {
-        // reserved[1]: experiment switch for the CTA shape (0 = default)
-        const uint32_t shape = p->reserved[1];
-        // default: 1024 threads x 2 rays (32 warps per SM hide the shading phases best; measured 94 ms vs 102 ms for 512 x 4
-        // at 1080p x 128 spp), falling back to 512 x 4 and then to the first-generation kernel as shared memory runs out
+      } else {
+        // 1024 threads x 2 rays (32 warps per SM hide the shading phases best; measured 94 ms vs 102 ms for 512 x 4 at
+        // 1080p x 128 spp) up to ~700 spheres, 512 x 4 up to ~1200 as the scene blob grows, then the first-generation kernel
+        // with 256 x 4 up to ~2400 spheres; beyond that VCRT_TRAVERSAL_BRUTE is refused (the LBVH is what large scenes are for)
+        bool launched = false;
+#ifdef VCRT_EXPERIMENTS
+        const uint32_t shape = p->reserved[1];   // CTA shape / kernel generation for A/B runs (tools/experiments/README.md)
+        launched = true;
         if (shape == 20 && scanWFits(1024, 1, 24)) rc = fixedMode ? launchScanW<1024, 1, 24, true>(args, &launches) : launchScanW<1024, 1, 24, false>(args, &launches);
         else if (shape == 21 && scanWFits(512, 2, 24)) rc = fixedMode ? launchScanW<512, 2, 24, true>(args, &launches) : launchScanW<512, 2, 24, false>(args, &launches);
-        else if ((shape == 0 || shape == 11) && scanUFits(1024, 1, 30)) rc = fixedMode ? launchScanU<1024, 1, 30, true>(args, &launches) : launchScanU<1024, 1, 30, false>(args, &launches);
-        else if ((shape == 0 || shape == 10) && scanUFits(512, 2, 30)) rc = fixedMode ? launchScanU<512, 2, 30, true>(args, &launches) : launchScanU<512, 2, 30, false>(args, &launches);
+        else if (shape == 10 && scanUFits(512, 2, 30)) rc = fixedMode ? launchScanU<512, 2, 30, true>(args, &launches) : launchScanU<512, 2, 30, false>(args, &launches);
         else if (shape == 12 && fixedMode && scanUFits(256, 4, 30)) rc = launchScanU<256, 4, 30, true>(args, &launches);
+        else if (shape == 1) rc = fixedMode ? (wide ? launchScan<512, 2, 12, true>(args, &launches) : launchScan<256, 2, 12, true>(args, &launches))
+                                            : (wide ? launchScan<512, 2, 12, false>(args, &launches) : launchScan<256, 2, 12, false>(args, &launches));
         else if (shape == 2 && fixedMode && scanFits(1024, 1, 12)) rc = launchScan<1024, 1, 12, true>(args, &launches);
         else if (shape == 3 && fixedMode && scanFits(768, 1, 12)) rc = launchScan<768, 1, 12, true>(args, &launches);
         else if (shape == 4 && fixedMode && scanFits(640, 1, 12)) rc = launchScan<640, 1, 12, true>(args, &launches);
-        else if (fixedMode) rc = wide ? launchScan<512, 2, 12, true>(args, &launches) : launchScan<256, 2, 12, true>(args, &launches);
-        else rc = wide ? launchScan<512, 2, 12, false>(args, &launches) : launchScan<256, 2, 12, false>(args, &launches);
+        else launched = false;
+#endif
+        if (launched) { }
+        else if (scanUFits(1024, 1, 30)) rc = fixedMode ? launchScanU<1024, 1, 30, true>(args, &launches) : launchScanU<1024, 1, 30, false>(args, &launches);
+        else if (scanUFits(512, 2, 30)) rc = fixedMode ? launchScanU<512, 2, 30, true>(args, &launches) : launchScanU<512, 2, 30, false>(args, &launches);
+        else rc = fixedMode ? launchScan<256, 2, 12, true>(args, &launches) : launchScan<256, 2, 12, false>(args, &launches);
         if (rc) return rc;
+      }
     }
     CUDA_TRY(cudaEventRecord(cudaComputeEvents[2], cudaComputeStream));
 
     const unsigned int pixelBlocks = (pixels + 255) / 256;
-    if (fixedMode && p->maxDepth != 0) fixed_to_float_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeAccumulated, cudaComputeFixedSums, pixels);
+    if (fixedMode) fixed_to_float_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeAccumulated, cudaComputeFixedSums, pixels);
     else combine_planes_kernel<<<pixelBlocks, 256, 0, cudaComputeStream>>>(cudaComputeAccumulated, cudaComputeSumPlanes, pixels, chunks, keep ? 1 : 0);
     launches++;
-    const bool fixedSums = fixedMode && p->maxDepth != 0;
+    const bool fixedSums = fixedMode;
     cudaComputeAccumulatedSamples = (keep ? cudaComputeAccumulatedSamples : 0) + p->samplesPerPixel;
     cudaComputeAccumulatedIsFixed = fixedMode;
 
@@ -812,7 +906,7 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         const void* src = fixedSums ? (const void*)cudaComputeFixedSums : (const void*)cudaComputeAccumulated;
         void* dst = fixedSums ? (void*)cudaComputeFixedReduced : (void*)cudaComputeReduced;
         const ncclDataType_t type = fixedSums ? ncclInt64 : ncclFloat;
-        const size_t elements = (size_t)pixels * 4;
+        const size_t elements = (size_t)pixels * (fixedSums ? (size_t)kFixedLanes : 4u);   // C3: 199 MB of int64 sums (float4 sums: 133 MB)
         if (p->flags & VCRT_FLAG_ALL_REDUCE) NCCL_TRY(pNcclAllReduce(src, dst, elements, type, ncclSum, cudaComputeComm, cudaComputeStream));
         else NCCL_TRY(pNcclReduce(src, dst, elements, type, ncclSum, 0, cudaComputeComm, cudaComputeStream));
         finalSums = cudaComputeReduced; finalFixed = cudaComputeFixedReduced;
@@ -898,6 +992,8 @@ extern "C" int cudaDestroyRenderer(void) {
     cudaComputeBvhArena = nullptr; cudaComputeBvhArenaBytes = 0; cudaComputeBvhReady = false;
     if (cudaComputeHostShape) delete[] cudaComputeHostShape;
     cudaComputeHostShape = nullptr;
+    if (cudaComputeHostBlob) free(cudaComputeHostBlob);
+    cudaComputeHostBlob = nullptr; cudaComputeHostBlobBytes = 0; cudaComputeSceneBlobCapacity = 0;
     cudaComputeStream = nullptr; for (int i = 0; i < 4; i++) cudaComputeEvents[i] = nullptr;
     cudaComputeImageWidth = cudaComputeImageHeight = 0; cudaComputeAccumulatedSamples = 0;
     cudaComputeImageValid = false; cudaComputeSceneReady = false; cudaComputeDeviceReady = false;

@@ -127,7 +127,7 @@ struct RenderArgs {
     uint32_t chunks;        // a pixel's spp split into this many work items (partial-sum planes)
     uint32_t flags;
     float4* sums;           // float modes: [chunks][height*width] (x,y,z = sums, w unused)
-    long long* fixedSums;   // fixed-point mode: [height*width][4] signed 32.32 sums (r, g, b, unused)
+    long long* fixedSums;   // fixed-point mode: [height*width][kFixedLanes] signed 32.32 sums (r, g, b)
     ItemPlan plan;
     uint32_t semantics;       // 0 = the reference shader as it is, 1 = BOOK (vcrt_shade.cuh)
     unsigned long long* counters;  // see Counter enum
@@ -180,5 +180,16 @@ VCRT_DEV bool tame_ray(float dd, float oo) { return dd > kTameDirMin2 && dd < kT
 constexpr float kTMin = 0.001f;   // functions.glsl:75
 constexpr float kTMax = 1e5f;     // globals.glsl:26 `infinity`
 constexpr float kFixedOne = 4294967296.0f;   // 2^32: radiance sums are exact integers in units of 2^-32
+constexpr int kFixedLanes = 3;               // r, g, b: alpha is the constant 1 of shader.comp:44 and never summed
+
+// shader.comp:53 `color.rgb += ray_color(r)` in 32.32 fixed point: three 64-bit REDs, associative, so the image does not depend
+// on the schedule or the GPU count.  The caller guarantees 0 <= result <= 1 per channel (cudaUploadScene only allows this
+// accumulator for scenes whose attenuations are in [0, 1]), so a sum of 2^24 samples x 8 ranks stays far below 2^63.
+VCRT_DEV void add_fixed(long long* fixedSums, uint32_t pixel, V3 result) {
+    unsigned long long* acc = reinterpret_cast<unsigned long long*>(fixedSums) + kFixedLanes * (size_t)pixel;
+    if (result.x != 0.f) atomicAdd(acc + 0, (unsigned long long)__float2ll_rn(result.x * kFixedOne));
+    if (result.y != 0.f) atomicAdd(acc + 1, (unsigned long long)__float2ll_rn(result.y * kFixedOne));
+    if (result.z != 0.f) atomicAdd(acc + 2, (unsigned long long)__float2ll_rn(result.z * kFixedOne));
+}
 
 }  // namespace vcrt

@@ -285,13 +285,14 @@ __global__ void __launch_bounds__(THREADS, 1) render_scan_kernel(const unsigned 
                 HitRec rec; rec.t = kTMax; rec.index = -1;
                 const uint32_t nc = CNT(r);
                 const bool exhaustive = nc > (uint32_t)CAP;
+                const bool tame = tame_ray(fmaf(ray.d.x, ray.d.x, fmaf(ray.d.y, ray.d.y, ray.d.z * ray.d.z)), fmaf(ray.o.x, ray.o.x, fmaf(ray.o.y, ray.o.y, ray.o.z * ray.o.z)));   // as make_filter
                 nRays++;
                 if (exhaustive) nOverflow++; else nCand += nc;
                 // candidates in scan order, then the "always" spheres (device indices scanCount..count-1)
                 const int nScan = exhaustive ? scanCount : (int)nc, nAll = nScan + (count - scanCount);
                 for (int e = 0; e < nAll; e++) {
                     const int j = e >= nScan ? scanCount + (e - nScan) : (exhaustive ? e : (int)LIST(e, r));
-                    hit_exact(sShape[j], j, ray, a, rec);
+                    hit_exact(sShape[j], j, ray, a, rec, tame);
                 }
                 V3 colour = v3(STF(SF_CR, r), STF(SF_CG, r), STF(SF_CB, r));
                 V3 result = v3(0.f, 0.f, 0.f);   // black: bug B7 (depth exhausted) and absorbed bad materials
@@ -325,10 +326,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scan_kernel(const unsigned 
                     uint32_t s = ST(SF_SAMPLE, r);
                     const uint32_t s1 = ST(SF_END, r);
                     if (FIXED) {
-                        long long* acc = args.fixedSums + 4 * (size_t)pixel;
-                        if (result.x != 0.f) atomicAdd((unsigned long long*)acc + 0, (unsigned long long)__float2ll_rn(result.x * kFixedOne));
-                        if (result.y != 0.f) atomicAdd((unsigned long long*)acc + 1, (unsigned long long)__float2ll_rn(result.y * kFixedOne));
-                        if (result.z != 0.f) atomicAdd((unsigned long long*)acc + 2, (unsigned long long)__float2ll_rn(result.z * kFixedOne));
+                        add_fixed(args.fixedSums, pixel, result);
                         s++;
                     } else {
                         const uint32_t chunk = (s1 - 1u) / sppPerChunk, s0 = chunk * sppPerChunk;

@@ -214,14 +214,15 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                 Ray ray; ray.o = v3(STF(SF_OX, r), STF(SF_OY, r), STF(SF_OZ, r)); ray.d = v3(STF(SF_DX, r), STF(SF_DY, r), STF(SF_DZ, r));
                 const float a = vdot(ray.d, ray.d);
                 HitRec rec; rec.t = kTMax; rec.index = -1;
-                const bool exhaustive = overflow || ((exhaustMask >> r) & 1u);
+                const bool tame = !((exhaustMask >> r) & 1u);
+                const bool exhaustive = overflow || !tame;
                 nRays++;
                 if (exhaustive) nOverflow++; else nCand += listCount;
                 // candidates in ascending scan order, then the "always" spheres (device indices scanCount..count-1)
                 const int nScan = exhaustive ? scanCount : (int)listCount, nAll = nScan + (count - scanCount);
                 for (int e = 0; e < nAll; e++) {
                     const int j = e >= nScan ? scanCount + (e - nScan) : (exhaustive ? e : (int)TLIST(e));
-                    hit_exact(sShape[j], j, ray, a, rec);
+                    hit_exact(sShape[j], j, ray, a, rec, tame);
                 }
                 V3 colour = v3(STF(SF_CR, r), STF(SF_CG, r), STF(SF_CB, r));
                 V3 result = v3(0.f, 0.f, 0.f);   // black: bug B7 (depth exhausted) and absorbed bad materials
@@ -255,10 +256,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                     uint32_t s = ST(SF_SAMPLE, r);
                     const uint32_t s1 = ST(SF_END, r);
                     if (FIXED) {
-                        long long* acc = args.fixedSums + 4 * (size_t)pixel;
-                        if (result.x != 0.f) atomicAdd((unsigned long long*)acc + 0, (unsigned long long)__float2ll_rn(result.x * kFixedOne));
-                        if (result.y != 0.f) atomicAdd((unsigned long long*)acc + 1, (unsigned long long)__float2ll_rn(result.y * kFixedOne));
-                        if (result.z != 0.f) atomicAdd((unsigned long long*)acc + 2, (unsigned long long)__float2ll_rn(result.z * kFixedOne));
+                        add_fixed(args.fixedSums, pixel, result);
                         s++;
                     } else {
                         const uint32_t chunk = (s1 - 1u) / sppPerChunk, s0 = chunk * sppPerChunk;

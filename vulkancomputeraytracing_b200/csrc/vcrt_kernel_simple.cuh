@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(128) render_simple_kernel(DeviceScene scene, R
                 rays++;
                 HitRec rec; rec.t = kTMax; rec.index = -1;
                 const float a = vdot(ray.d, ray.d);
-                for (int i = 0; i < scene.count; i++) hit_exact(__ldg(&scene.shape[i]), i, ray, a, rec);
+                for (int i = 0; i < scene.count; i++) hit_exact(__ldg(&scene.shape[i]), i, ray, a, rec, false);
                 if (rec.index < 0) {
                     if (args.flags & kFlagCountStats) atomicAdd(&args.counters[CTR_PATH0 + min(pass, 7u)], 1ull);
                     result = vmul(colour, sky(ray.d)); finished = true; break;

@@ -6,12 +6,15 @@
 */
 #pragma once
 #include "vcrt_device.cuh"
+#include "vcrt_powf.cuh"
 
 namespace vcrt {
 
 // functions.glsl:14-33 for one sphere, `a` = dot(d,d) hoisted by the caller (same value every
 // time the reference recomputes it).  Updates rec when this sphere gives a nearer accepted root.
-VCRT_DEV void hit_exact(float4 shape, int index, const Ray& r, float a, HitRec& rec) {
+// `shortcut`: the ray is tame (tame_ray, vcrt_device.cuh), which is what the early reject below is proven for; the exhaustive
+// scans of non-tame rays and the in-order cross-check kernel pass false and run the reference's statements literally.
+VCRT_DEV void hit_exact(float4 shape, int index, const Ray& r, float a, HitRec& rec, bool shortcut) {
     V3 oc = vsub(r.o, v3(shape.x, shape.y, shape.z));
     float half_b = vdot(oc, r.d);
     float c = fsub(vdot(oc, oc), fmul(shape.w, shape.w));
@@ -20,8 +23,9 @@ VCRT_DEV void hit_exact(float4 shape, int index, const Ray& r, float a, HitRec& 
     // Moving away from a sphere we are not inside (half_b > 0, c >= 0): a*c >= 0 gives disc <= fl(half_b^2), and
     // sqrt(fl(x*x)) == |x| exactly in round-to-nearest binary arithmetic, so sqrtd <= half_b and both numerators are <= 0:
     // the reference rejects both roots against t_min.  Same outcome, without the square root and the two divisions
-    // (this is every ray leaving the surface it just scattered from, and every sphere behind the origin).
-    if (half_b > 1e-18f && c >= 0.f) return;   // 1e-18: half_b^2 stays a normal number, which the sqrt identity needs
+    // (this is every ray leaving the surface it just scattered from, and every sphere behind the origin).  Not for rays whose
+    // half_b^2 or a*c may overflow: inf - inf = NaN passes `disc < 0`, the reference then accepts the sphere at t = NaN.
+    if (shortcut && half_b > 1e-18f && c >= 0.f) return;   // 1e-18: half_b^2 stays a normal number, which the sqrt identity needs
     float sqrtd = fsqrt(disc);
     float root = fdiv(fsub(-half_b, sqrtd), a);
     if (root <= kTMin || rec.t <= root) {
@@ -66,15 +70,17 @@ VCRT_DEV bool modified_refract(V3 v, V3 n, float ni_over_nt, V3& refracted) {
     return false;
 }
 
-// functions.glsl:58-62.  pow(x, 5.) as four multiplies: same sign and NaN behaviour as C powf
-// for the negative bases the unnormalised cosine produces (bug B6 -> "refract").
+// functions.glsl:58-62.  pow(x, 5.) carries the bits of C powf as the reference build evaluates it (vcrt_powf.cuh): three
+// binary32 multiplies differ from that by an ulp on half of the inputs, which flips `rand < reflect_prob` now and then.
+// A negative base (bug B6: 90 % of the calls, the cosine is an unnormalised dot product) gives a negative power, so the
+// caller's test is false and the ray refracts, as in the oracle.  One binary64 chain per refracting glass hit.
+// Out of line: the binary64 chain would otherwise raise the register count of every kernel for a routine that one ray in
+// twenty reaches (inlined: 44 bytes of spills in the brute-force kernel at its 64-register budget).
+__device__ __noinline__ float powf5_call(float x) { return powf5(x); }
 VCRT_DEV float schlick(float cosine, float ior) {
     float r0 = fdiv(fsub(1.f, ior), fadd(1.f, ior));
     r0 = fmul(r0, r0);
-    float x = fsub(1.f, cosine);
-    float x2 = fmul(x, x);
-    float x5 = fmul(fmul(x2, x2), x);
-    return fadd(r0, fmul(fsub(1.f, r0), x5));
+    return fadd(r0, fmul(fsub(1.f, r0), powf5_call(fsub(1.f, cosine))));
 }
 
 // textures.glsl:19-71.  Scatters `ray` at a hit on sphere `index` at parameter t; multiplies

@@ -57,7 +57,7 @@ def render_params(width, height, spp, depth=50, seed=0, sample_offset=0, travers
     cabi.load().vcrtDefaultRenderParams(ctypes.byref(p))
     p.width, p.height, p.samplesPerPixel, p.maxDepth, p.seed = width, height, spp, depth, seed
     p.sampleOffset, p.traversal, p.flags, p.sampleChunks, p.totalSamples = sample_offset, traversal, flags, sample_chunks, total_samples
-    p.reserved[1] = shape
+    p.reserved[1] = shape   # experiments build only (tools/experiments/README.md); the product rejects non-zero reserved fields
     p.semantics = semantics
     return p
 

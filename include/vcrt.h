@@ -118,7 +118,7 @@ typedef struct VcrtRenderStats {
     uint32_t kernelLaunches;   /* kernels this call launched */
     uint32_t traversalUsed;    /* VCRT_TRAVERSAL_* actually run */
     uint32_t sampleChunksUsed;
-    uint32_t reserved;
+    uint32_t checkFailures;    /* bounds checks that failed; always 0 unless the library was built with -DVCRT_CHECKED (tools/checked_run.py) */
 } VcrtRenderStats;
 
 void vcrtDefaultRenderParams(OUT VcrtRenderParams* params);

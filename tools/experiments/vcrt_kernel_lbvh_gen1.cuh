@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_kernel(BvhScene 
             }
             if (!finished) nExhausted++;
             if (FIXED) {
-                add_fixed(args.fixedSums, pixel, result);
+                add_fixed(args, pixel, result);
             } else sum = vadd(sum, result);
         }
         if (!FIXED) args.sums[(size_t)chunk * pixels + pixel] = make_float4(sum.x, sum.y, sum.z, 0.f);

@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanw_kernel(const unsigned
                 uint32_t s = WS(WF_SAMPLE, r, t);
                 const uint32_t s1 = WS(WF_END, r, t);
                 if (FIXED) {
-                    add_fixed(args.fixedSums, pixel, result);
+                    add_fixed(args, pixel, result);
                     s++;
                 } else {
                     const uint32_t chunk = (s1 - 1u) / sppPerChunk, s0 = chunk * sppPerChunk;

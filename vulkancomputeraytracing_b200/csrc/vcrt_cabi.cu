@@ -937,6 +937,7 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     CUDA_TRY(cudaEventElapsedTime(&st.renderKernelMs, cudaComputeEvents[1], cudaComputeEvents[2]));
     CUDA_TRY(cudaEventElapsedTime(&st.totalMs, cudaComputeEvents[0], cudaComputeEvents[3]));
     st.kernelLaunches = launches; st.traversalUsed = traversal; st.sampleChunksUsed = chunks;
+    st.checkFailures = (uint32_t)(ctr[CTR_CHECK_FAILED] > 0xffffffffull ? 0xffffffffull : ctr[CTR_CHECK_FAILED]);
     if (st.badMaterial) return fail(VCRT_ERROR_SCENE, "scene has texture ids outside 1..3 (hits on them were absorbed)%s", "");
     return VCRT_SUCCESS;
 }

@@ -135,7 +135,16 @@ struct RenderArgs {
 };
 
 enum Counter { CTR_RAYS = 0, CTR_EXHAUSTED, CTR_BAD_MATERIAL, CTR_CANDIDATES, CTR_OVERFLOWS, CTR_TESTS, CTR_NODES,
-               CTR_HITS0, CTR_HITS1, CTR_HITS2, CTR_HITS3, CTR_PATH0, CTR_COUNT = CTR_PATH0 + 8 };
+               CTR_HITS0, CTR_HITS1, CTR_HITS2, CTR_HITS3, CTR_PATH0, CTR_CHECK_FAILED = CTR_PATH0 + 8, CTR_COUNT };
+
+// Bounds checks of our own (compute-sanitizer is closed on the GPU pool): with -DVCRT_CHECKED every hand-computed index into
+// shared, local or global memory is compared with its bound before use and violations are counted (VcrtRenderStats.checkFailures,
+// tools/checked_run.py); the access is then skipped or clamped.  The product build compiles the checks away.
+#ifdef VCRT_CHECKED
+#define VCRT_CHECK(counters, cond) ((cond) ? true : (atomicAdd(&(counters)[CTR_CHECK_FAILED], 1ull), false))
+#else
+#define VCRT_CHECK(counters, cond) (true)
+#endif
 
 // x / d given inv <= 1 / d (rounded down), for quotients below 2^22 and d below 2^24: the float estimate never exceeds the
 // quotient and is at most 2 short of it
@@ -185,8 +194,10 @@ constexpr int kFixedLanes = 3;               // r, g, b: alpha is the constant 1
 // shader.comp:53 `color.rgb += ray_color(r)` in 32.32 fixed point: three 64-bit REDs, associative, so the image does not depend
 // on the schedule or the GPU count.  The caller guarantees 0 <= result <= 1 per channel (cudaUploadScene only allows this
 // accumulator for scenes whose attenuations are in [0, 1]), so a sum of 2^24 samples x 8 ranks stays far below 2^63.
-VCRT_DEV void add_fixed(long long* fixedSums, uint32_t pixel, V3 result) {
-    unsigned long long* acc = reinterpret_cast<unsigned long long*>(fixedSums) + kFixedLanes * (size_t)pixel;
+VCRT_DEV void add_fixed(const RenderArgs& args, uint32_t pixel, V3 result) {
+    // (checked build) the pixel is inside the image, the radiance in [0, 1] - what keeps the integer sums from overflowing
+    if (!VCRT_CHECK(args.counters, pixel < args.width * args.height && result.x >= 0.f && result.x <= 1.f && result.y >= 0.f && result.y <= 1.f && result.z >= 0.f && result.z <= 1.f)) return;
+    unsigned long long* acc = reinterpret_cast<unsigned long long*>(args.fixedSums) + kFixedLanes * (size_t)pixel;
     if (result.x != 0.f) atomicAdd(acc + 0, (unsigned long long)__float2ll_rn(result.x * kFixedOne));
     if (result.y != 0.f) atomicAdd(acc + 1, (unsigned long long)__float2ll_rn(result.y * kFixedOne));
     if (result.z != 0.f) atomicAdd(acc + 2, (unsigned long long)__float2ll_rn(result.z * kFixedOne));

@@ -111,7 +111,7 @@ constexpr float kLbvhK = LBVH_K_EPS * 5.9604644775390625e-08f;   // K = 32 eps (
 VCRT_DEV float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 VCRT_DEV float sqrt_approx(float x) { float r; asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
-struct LbvhCounts { uint32_t rays, nodes, tests, exhausted, bad; };
+struct LbvhCounts { uint32_t rays, nodes, tests, exhausted, bad; unsigned long long* counters; };
 
 VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, OrderedHit& rec, int* stack, LbvhCounts& n) {
     const float oo = fmaf(ray.o.x, ray.o.x, fmaf(ray.o.y, ray.o.y, ray.o.z * ray.o.z));
@@ -174,6 +174,7 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
     for (;;) {
         if (node >= 0) {
             n.nodes++;
+            if (!VCRT_CHECK(n.counters, (uint32_t)node < scene.treeCount - 1u)) break;
             const float4 na = __ldg(&nodes[first + (uint32_t)node].a), nb = __ldg(&nodes[first + (uint32_t)node].b), nc = __ldg(&nodes[first + (uint32_t)node].c);
             const int2 ch = __ldg(reinterpret_cast<const int2*>(&nodes[first + (uint32_t)node].child0));
             // child0: near (na.x, na.y, na.z) far (na.w, nb.x, nb.y); child1: near (nb.z, nb.w, nc.x) far (nc.y, nc.z, nc.w)
@@ -186,12 +187,13 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
             if (h0 && h1) {
                 const bool swap = n1 < n0;
                 node = swap ? ch.y : ch.x;
-                stack[sp++] = swap ? ch.x : ch.y;
+                if (VCRT_CHECK(n.counters, sp < 64)) stack[sp++] = swap ? ch.x : ch.y;
                 continue;
             }
             if (h0 || h1) { node = h0 ? ch.x : ch.y; continue; }
         } else {
             const int l = ~node;
+            if (!VCRT_CHECK(n.counters, l >= 0 && (uint32_t)l < scene.treeCount)) break;
             hit_ordered(__ldg(&scene.leafShape[l]), (int)__ldg(&scene.leafDevice[l]), __ldg(&scene.leafOrig[l]), ray, a, rec);
             n.tests++;
         }
@@ -205,7 +207,7 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhS
     const uint32_t pixels = args.width * args.height;
     const uint32_t sppPerChunk = args.plan.sppPerRun;   // host-made plan (vcrt_device.cuh)
     const uint32_t tilesX = args.plan.tilesX, totalItems = args.plan.totalItems;
-    LbvhCounts n = {0u, 0u, 0u, 0u, 0u};
+    LbvhCounts n = {0u, 0u, 0u, 0u, 0u, args.counters};
     int stack[65];
 
     const uint32_t firstDynamic = gridDim.x * blockDim.x;
@@ -225,7 +227,7 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhS
             for (;;) {
                 if (haveRun && s < s1) break;
                 if (haveRun) {
-                    if (!FIXED) args.sums[(size_t)chunk * pixels + pixel] = make_float4(sum.x, sum.y, sum.z, 0.f);
+                    if (!FIXED && VCRT_CHECK(args.counters, chunk < args.chunks && pixel < pixels)) args.sums[(size_t)chunk * pixels + pixel] = make_float4(sum.x, sum.y, sum.z, 0.f);
                     haveRun = false;
                 }
                 if (!firstItem) item = firstDynamic + atomicAdd(args.workCounter, 1u);   // (an explicit warp-aggregated claim is 1.3 % slower)
@@ -281,7 +283,7 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhS
         }
         if (!inFlight) {
             if (FIXED) {
-                add_fixed(args.fixedSums, pixel, result);
+                add_fixed(args, pixel, result);
             } else sum = vadd(sum, result);
         }
     }

@@ -292,7 +292,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scan_kernel(const unsigned 
                 const int nScan = exhaustive ? scanCount : (int)nc, nAll = nScan + (count - scanCount);
                 for (int e = 0; e < nAll; e++) {
                     const int j = e >= nScan ? scanCount + (e - nScan) : (exhaustive ? e : (int)LIST(e, r));
-                    hit_exact(sShape[j], j, ray, a, rec, tame);
+                    if (VCRT_CHECK(args.counters, j >= 0 && j < count && (exhaustive || e >= nScan || e < CAP))) hit_exact(sShape[j], j, ray, a, rec, tame);
                 }
                 V3 colour = v3(STF(SF_CR, r), STF(SF_CG, r), STF(SF_CB, r));
                 V3 result = v3(0.f, 0.f, 0.f);   // black: bug B7 (depth exhausted) and absorbed bad materials
@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scan_kernel(const unsigned 
                     uint32_t s = ST(SF_SAMPLE, r);
                     const uint32_t s1 = ST(SF_END, r);
                     if (FIXED) {
-                        add_fixed(args.fixedSums, pixel, result);
+                        add_fixed(args, pixel, result);
                         s++;
                     } else {
                         const uint32_t chunk = (s1 - 1u) / sppPerChunk, s0 = chunk * sppPerChunk;
@@ -334,7 +334,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scan_kernel(const unsigned 
                         sum = vadd(sum, result);
                         s++;
                         if (s < s1) { ST(SF_SUMR, r) = __float_as_uint(sum.x); ST(SF_SUMG, r) = __float_as_uint(sum.y); ST(SF_SUMB, r) = __float_as_uint(sum.z); }
-                        else args.sums[(size_t)chunk * planeStride + pixel] = make_float4(sum.x, sum.y, sum.z, 0.f);   // the item's only global write
+                        else if (VCRT_CHECK(args.counters, chunk < args.chunks && pixel < planeStride)) args.sums[(size_t)chunk * planeStride + pixel] = make_float4(sum.x, sum.y, sum.z, 0.f);   // the item's only global write
                     }
                     if (s < s1) { ST(SF_SAMPLE, r) = s; needStart = true; } else needClaim = true;
                 }

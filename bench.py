@@ -47,10 +47,12 @@ WORKLOADS = {
     "c5": (1920, 1080, 256, 50, "stress", "configs[4]: all metal/dielectric divergence stress scene, 1920x1080, 256 spp, depth 50"),
 }
 FLOP_PER_TEST = 17      # one ray-sphere test of the reference = 17 flop (11 FP32-pipe instructions)
-FLOP_PER_FILTER = 14    # what the brute-force kernel executes per (ray, sphere): 7 FMAs of the conservative filter
+FLOP_PER_FILTER = 14    # what the path kernel executes per (ray, sphere): 7 FMAs of the conservative filter
+FLOP_PER_PRIMARY_FILTER = 8   # what the primary-visibility kernel executes per (camera ray, sphere): 3 FMAs / multiplies + 1 multiply
 FLOP_PER_BOX = 24       # LBVH: one box = 6 FMAs + 6 min/max, counted as 2 x 6 + 6 x 2
 TRAVERSALS = {"auto": 0, "brute": 1, "lbvh": 2, "simple": 3}
 KERNEL_NAMES = {1: "render_scanu_kernel", 2: "render_lbvh_flat_kernel", 3: "render_simple_kernel"}
+PRIMARY_KERNEL = "primary_scan_kernel"
 CPU_BUILD = "g++ -O3 -march=x86-64-v3 -fopenmp, FMA contraction on (not the bit-stable -O2 -ffp-contract=off build the goldens come from)"
 
 
@@ -219,7 +221,7 @@ class Bench:
             time.sleep(0.3)
         if collective:
             self.barrier()   # after the sampler start-up: a late rank would otherwise make the others wait inside their first reduce
-        tot = {"dev_ms": 0.0, "kernel_ms": 0.0, "rays": 0, "launches": 0, "cand": 0, "nodes": 0, "tests": 0}
+        tot = {"dev_ms": 0.0, "kernel_ms": 0.0, "rays": 0, "launches": 0, "cand": 0, "nodes": 0, "tests": 0, "primary_ms": 0.0, "primary_rays": 0}
         t0 = time.perf_counter()
         for _ in range(steps):
             cabi.check(lib.cudaFlushL2())
@@ -230,6 +232,7 @@ class Bench:
             st = self.host.stats()
             tot["dev_ms"] += ms.value; tot["kernel_ms"] += st.renderKernelMs; tot["rays"] += st.rays; tot["launches"] += st.kernelLaunches
             tot["cand"] += st.candidates; tot["nodes"] += st.nodeVisits; tot["tests"] += st.sphereTests
+            tot["primary_ms"] += st.primaryKernelMs; tot["primary_rays"] += st.primaryRays
         tot["wall_s"] = time.perf_counter() - t0
         if collective:
             self.barrier()
@@ -312,14 +315,33 @@ def roofline(b, leg, name):
            "ffma_only_kernel_tflops": ffma_tf, "kernel_ms_per_step": leg["kernel_ms_per_step"],
            "kernel_share_of_step": raw["kernel_ms"] / raw["dev_ms"] if raw["dev_ms"] else None, "traffic": None}
     if raw["used"] == 1:
-        tests = raw["rays"] * raw["count"]
-        out["achieved"] = tests * FLOP_PER_TEST / kernel_s * 1e-12
-        out["algorithmic"] = f"rays x {raw['count']} spheres x {FLOP_PER_TEST} flop (SURVEY.md 8d: the reference's test with a and r^2 hoisted); rays from the in-kernel counter, this rank"
-        executed = (tests * FLOP_PER_FILTER + raw["cand"] * FLOP_PER_TEST) / kernel_s * 1e-12
+        # Two kernels share a brute-force step: primary_scan_kernel (camera rays + first scatter event) and render_scanu_kernel (every
+        # other ray).  The roofline object is that of the DOMINANT one, the path kernel, from its own CUDA-event time; the primary
+        # kernel and the step as a whole ride beside it.
+        n = raw["count"]
+        p_rays, p_s = raw["primary_rays"], raw["primary_ms"] * 1e-3
+        s_rays, s_s = raw["rays"] - p_rays, kernel_s - p_s
+        out["kernel_ms_per_step"] = s_s * 1e3 / leg["steps"]
+        out["kernel_share_of_step"] = s_s * 1e3 / raw["dev_ms"] if raw["dev_ms"] else None
+        out["achieved"] = s_rays * n * FLOP_PER_TEST / s_s * 1e-12
+        out["algorithmic"] = (f"rays of this kernel x {n} spheres x {FLOP_PER_TEST} flop (SURVEY.md 8d: the reference's test with a and r^2 hoisted); "
+                              "rays from the in-kernel counters, this rank; time = CUDA events around this kernel's launches")
+        # candidates are counted over both kernels; split them by the rays each kernel traced
+        cand_s = raw["cand"] * s_rays / max(1, raw["rays"])
+        executed = (s_rays * n * FLOP_PER_FILTER + cand_s * FLOP_PER_TEST) / s_s * 1e-12
         out["achieved_executed"] = executed
         out["frac_executed"] = executed / peak
         out["executed"] = f"what the kernel issues: {FLOP_PER_FILTER} flop (7 FMAs of the conservative filter) per (ray, sphere) + {FLOP_PER_TEST} per exact test of a survivor; shading not counted"
         out["filter_candidates_per_ray"] = leg.get("filter_candidates_per_ray")
+        if p_rays and p_s > 0:
+            out["primary_kernel"] = {"kernel": PRIMARY_KERNEL, "kernel_ms_per_step": p_s * 1e3 / leg["steps"], "share_of_step": p_s * 1e3 / raw["dev_ms"],
+                                     "rays_per_step": p_rays / leg["steps"], "achieved": p_rays * n * FLOP_PER_TEST / p_s * 1e-12,
+                                     "frac": p_rays * n * FLOP_PER_TEST / p_s * 1e-12 / peak,
+                                     "frac_executed": p_rays * n * FLOP_PER_PRIMARY_FILTER / p_s * 1e-12 / peak,
+                                     "executed": f"{FLOP_PER_PRIMARY_FILTER} flop per (camera ray, sphere): the camera-relative filter"}
+        out["step"] = {"kernels": [PRIMARY_KERNEL, leg["kernel"]] if p_rays else [leg["kernel"]], "kernel_ms_per_step": kernel_s * 1e3 / leg["steps"],
+                       "achieved": raw["rays"] * n * FLOP_PER_TEST / kernel_s * 1e-12, "frac": raw["rays"] * n * FLOP_PER_TEST / kernel_s * 1e-12 / peak,
+                       "note": "all rays of the step x spheres x 17 flop over the time of both kernels: the algorithmic rate of the brute-force path as a whole"}
     else:
         flop = raw["nodes"] * 2 * FLOP_PER_BOX + raw["tests"] * FLOP_PER_TEST
         out["achieved"] = flop / kernel_s * 1e-12

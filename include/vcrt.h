@@ -119,6 +119,9 @@ typedef struct VcrtRenderStats {
     uint32_t traversalUsed;    /* VCRT_TRAVERSAL_* actually run */
     uint32_t sampleChunksUsed;
     uint32_t checkFailures;    /* bounds checks that failed; always 0 unless the library was built with -DVCRT_CHECKED (tools/checked_run.py) */
+    uint64_t primaryRays;      /* of `rays`: camera rays traced (and shaded) by the primary-visibility kernel; 0 where it does not run */
+    float primaryKernelMs;     /* of renderKernelMs: the primary-visibility kernel(s) */
+    uint32_t renderPasses;     /* launches of the path kernel this call was split into (sample sub-ranges) */
 } VcrtRenderStats;
 
 void vcrtDefaultRenderParams(OUT VcrtRenderParams* params);

@@ -62,7 +62,7 @@ def test_struct_layouts():
     assert ctypes.sizeof(cabi.VcrtCamera) == 40
     assert ctypes.sizeof(cabi.VcrtRenderParams) == 56 and cabi.VcrtRenderParams.semantics.offset == 52
     assert cabi.VcrtRenderParams.seed.offset == 16 and cabi.VcrtRenderParams.sampleOffset.offset == 24
-    assert ctypes.sizeof(cabi.VcrtRenderStats) == 8 * 8 + 4 * 8 + 8 * 8 + 6 * 4
+    assert ctypes.sizeof(cabi.VcrtRenderStats) == 8 * 8 + 4 * 8 + 8 * 8 + 6 * 4 + 8 + 2 * 4
     assert ctypes.sizeof(cabi.VcrtSceneRecipe) == 24
 
 

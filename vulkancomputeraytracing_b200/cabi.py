@@ -49,7 +49,8 @@ class VcrtRenderStats(ctypes.Structure):
                 ("candidates", ctypes.c_uint64), ("listOverflows", ctypes.c_uint64),
                 ("hitsByMaterial", ctypes.c_uint64 * 4), ("pathLength", ctypes.c_uint64 * 8),
                 ("renderKernelMs", ctypes.c_float), ("totalMs", ctypes.c_float), ("kernelLaunches", ctypes.c_uint32),
-                ("traversalUsed", ctypes.c_uint32), ("sampleChunksUsed", ctypes.c_uint32), ("checkFailures", ctypes.c_uint32)]
+                ("traversalUsed", ctypes.c_uint32), ("sampleChunksUsed", ctypes.c_uint32), ("checkFailures", ctypes.c_uint32),
+                ("primaryRays", ctypes.c_uint64), ("primaryKernelMs", ctypes.c_float), ("renderPasses", ctypes.c_uint32)]
 
 
 class VcrtSceneRecipe(ctypes.Structure):

@@ -11,6 +11,7 @@
 #include "vcrt_kernel_scan.cuh"
 #include "vcrt_kernel_lbvh.cuh"
 #include "vcrt_kernel_scanu.cuh"
+#include "vcrt_kernel_primary.cuh"
 #ifdef VCRT_EXPERIMENTS   // A/B kernels that no default call reaches: tools/experiments/README.md (build with VCRT_EXTRA_NVCC=-DVCRT_EXPERIMENTS)
 #include "../../tools/experiments/vcrt_kernel_scanw.cuh"
 #include "../../tools/experiments/vcrt_kernel_lbvh_gen1.cuh"
@@ -37,6 +38,9 @@ static bool cudaComputeDeviceReady = false;
 static int cudaComputeSmCount = 0;
 static cudaStream_t cudaComputeStream = nullptr;
 static cudaEvent_t cudaComputeEvents[4] = {nullptr, nullptr, nullptr, nullptr};
+static const uint32_t kMaxTimedPasses = 64;                 // primary-kernel time is measured for the first 64 launches of a call
+static cudaEvent_t cudaComputePassEvents[2 * kMaxTimedPasses];
+static uint32_t cudaComputePassEventCount = 0;
 
 static unsigned char* cudaComputeSceneBlob = nullptr;   // device copy of the SoA blob
 static SceneBlob cudaComputeSceneHeader;
@@ -67,6 +71,9 @@ static float4* cudaComputeResultImage = nullptr;        // [W*H] normalised RGBA
 static uint32_t cudaComputeImageWidth = 0, cudaComputeImageHeight = 0;
 static uint64_t cudaComputeAccumulatedSamples = 0;
 static bool cudaComputeImageValid = false;
+static float4* cudaComputePrimary = nullptr;            // PrimaryBuffer of one launch (vcrt_kernel_primary.cuh): plane a, then plane b
+static size_t cudaComputePrimaryCapacity = 0;           // entries (32 bytes each)
+static const size_t kPrimaryMaxEntries = (size_t)9 << 27;   // 36 GiB: configs[1] (1920 x 1080 x 500 = 1.04e9 samples, 33 GB) in one launch
 static unsigned long long* cudaComputeCounters = nullptr;
 static unsigned int* cudaComputeWorkCounter = nullptr;
 static VcrtRenderStats cudaComputeLastStats;
@@ -236,6 +243,21 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
             chot[j] = make_float4(s.center[0], s.center[1], s.center[2], f);
         }
         cudaError_t ce = cudaMemcpyToSymbolAsync(cSceneHot, chot, (size_t)scanPad * sizeof(float4), 0, cudaMemcpyHostToDevice, cudaComputeStream);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(cudaComputeStream);
+        // the primary-visibility scan (vcrt_kernel_primary.cuh): centres relative to the camera, (c', |c'|^2 - R2) with
+        // R2 = r^2 + kappa(|c'|^2 + r^2); c' is the binary64 difference rounded once, and |c'|^2 is taken from the ROUNDED c'
+        for (uint32_t j = 0; j < scanPad && ce == cudaSuccess; j++) {
+            if (j >= scanCount) { chot[j] = make_float4(0.f, 0.f, 0.f, INFINITY); continue; }
+            const VcrtSphere& s = spheres[order[j]];
+            const float rx = (float)((double)s.center[0] - (double)camera->lookfrom[0]), ry = (float)((double)s.center[1] - (double)camera->lookfrom[1]),
+                        rz = (float)((double)s.center[2] - (double)camera->lookfrom[2]);
+            const double cc = (double)rx * rx + (double)ry * ry + (double)rz * rz, r2 = (double)s.radius * s.radius;
+            const double bound = cc - (r2 + (double)kKappaU * (cc + r2)) * (1.0 + 1.0 / 4194304.0);
+            float f = (float)bound;
+            if ((double)f > bound) f = nextafterf(f, -INFINITY);   // rounded DOWN: can only let more spheres pass
+            chot[j] = make_float4(rx, ry, rz, f);
+        }
+        if (ce == cudaSuccess) ce = cudaMemcpyToSymbolAsync(cPrimaryHot, chot, (size_t)scanPad * sizeof(float4), 0, cudaMemcpyHostToDevice, cudaComputeStream);
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(cudaComputeStream);
         free(chot);
         if (ce != cudaSuccess) { free(host); delete[] order; return fail(VCRT_ERROR_CUDA, "scene table upload: %s", cudaGetErrorString(ce)); }
@@ -634,6 +656,19 @@ static int ensureBvh(void) {
     return VCRT_SUCCESS;
 }
 
+template <bool FIXED>
+static int launchPrimaryScan(const RenderArgs& args, uint32_t* launches) {
+    const size_t smem = primary_scan_smem(cudaComputeSceneHeader.bytes);
+    CUDA_TRY(cudaFuncSetAttribute(primary_scan_kernel<FIXED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int perSm = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, primary_scan_kernel<FIXED>, kPrimaryThreads, smem));
+    if (perSm < 1) perSm = 1;
+    primary_scan_kernel<FIXED><<<(unsigned int)(cudaComputeSmCount * perSm), kPrimaryThreads, smem, cudaComputeStream>>>(cudaComputeSceneBlob, args, (int)cudaComputeSceneHeader.scanPad);
+    CUDA_TRY(cudaGetLastError());
+    *launches += 1;
+    return VCRT_SUCCESS;
+}
+
 template <bool FIXED, bool STATS, bool FLAT>
 static int launchLbvh(const RenderArgs& args, uint32_t* launches) {
 #ifdef VCRT_EXPERIMENTS
@@ -789,13 +824,30 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         }
         return true;
     };
+    const bool traces = p->maxDepth != 0 && p->samplesPerPixel != 0;   // otherwise no kernel runs and the sums of this call are zero
+    // Primary visibility (vcrt_kernel_primary.cuh), brute force only: the camera rays of a launch and their first scatter events
+    // are done by a kernel of their own and handed to the path kernel through a buffer of 32 bytes per sample.  VCRT_NO_PRIMARY=1
+    // in the environment switches it off (A/B measurements); the first-generation brute-force kernel (scenes beyond ~1200
+    // spheres) does not use it, and for the LBVH it was measured to lose.
+    static const bool primaryDisabled = getenv("VCRT_NO_PRIMARY") && atoi(getenv("VCRT_NO_PRIMARY")) != 0;
+    bool usePrimary = traces && !primaryDisabled && traversal == VCRT_TRAVERSAL_BRUTE && scanUFits(512, 2, 30) &&
+                      primary_scan_smem(cudaComputeSceneHeader.bytes) <= kSmemBudget;
+#ifdef VCRT_EXPERIMENTS
+    if (p->reserved[1] != 0 && p->reserved[1] != 10 && p->reserved[1] != 12) usePrimary = false;   // only the product kernels read the buffer
+#endif
     uint32_t passes = 1u, perRunFixed = 1u;
+    if (usePrimary) {
+        const uint64_t entries = tilesAll * 32u * p->samplesPerPixel;
+        if (fixedMode) passes = (uint32_t)((entries + kPrimaryMaxEntries - 1) / kPrimaryMaxEntries);
+        else if (entries > kPrimaryMaxEntries) usePrimary = false;
+    }
     if (fixedMode) {
 #ifdef VCRT_EXPERIMENTS
         if (p->reserved[0]) perRunFixed = p->reserved[0];
 #endif
         const uint64_t items = tilesAll * 32u * ((p->samplesPerPixel + perRunFixed - 1u) / perRunFixed);
-        passes = (uint32_t)((items + kMaxItems - 1) / kMaxItems);
+        const uint32_t byItems = (uint32_t)((items + kMaxItems - 1) / kMaxItems);
+        if (passes < byItems) passes = byItems;
         const uint32_t byRuns = (p->samplesPerPixel / perRunFixed) / ((1u << 22) - 2u) + 1u;   // runs per pixel and launch stay below 2^22
         if (passes < byRuns) passes = byRuns;
         if (passes < 1u) passes = 1u;
@@ -807,8 +859,18 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     // Float modes: the kernels write one plane per run, and ceil(spp / ceil(spp / chunks)) can be smaller than the chunk count
     // asked for (7 samples in 5 chunks = 4 runs of 2): only the planes that are written may be summed.
     if (!fixedMode) chunks = plan.runsPerPixel;
-    const bool traces = p->maxDepth != 0 && p->samplesPerPixel != 0;   // otherwise no kernel runs and the sums of this call are zero
     rc = ensureImageBuffers(p->width, p->height, chunks ? chunks : 1u); if (rc) return rc;
+    if (usePrimary) {
+        const uint32_t passSppMax = fixedMode ? (p->samplesPerPixel + passes - 1u) / passes : p->samplesPerPixel;
+        const size_t need = (size_t)plan.pixelsPadded * passSppMax;
+        if ((uint64_t)plan.tiles * passSppMax >= (1ull << 31)) usePrimary = false;
+        else if (need > cudaComputePrimaryCapacity) {
+            if (cudaComputePrimary) cudaFree(cudaComputePrimary);
+            cudaComputePrimary = nullptr; cudaComputePrimaryCapacity = 0;
+            if (cudaMalloc(&cudaComputePrimary, need * 2 * sizeof(float4)) == cudaSuccess) cudaComputePrimaryCapacity = need;
+            else { cudaGetLastError(); cudaComputePrimary = nullptr; usePrimary = false; }   // no room: the path kernels trace their primary rays themselves
+        }
+    }
     const bool keep = (p->flags & VCRT_FLAG_ACCUMULATE) && cudaComputeAccumulatedSamples > 0;
     if (keep && fixedMode != cudaComputeAccumulatedIsFixed)
         return fail(VCRT_ERROR_UNSUPPORTED, "VCRT_FLAG_ACCUMULATE across different accumulation modes%s", "");
@@ -823,8 +885,10 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     args.chunks = chunks; args.flags = p->flags; args.sums = cudaComputeSumPlanes;
     args.fixedSums = cudaComputeFixedSums; args.plan = plan;
     args.counters = cudaComputeCounters; args.workCounter = cudaComputeWorkCounter;
+    args.primary.a = usePrimary ? cudaComputePrimary : nullptr;
+    args.primary.b = usePrimary ? cudaComputePrimary + cudaComputePrimaryCapacity : nullptr;
 
-    uint32_t launches = 0;
+    uint32_t launches = 0, timedPasses = 0;
     CUDA_TRY(cudaEventRecord(cudaComputeEvents[0], cudaComputeStream));
     CUDA_TRY(cudaMemsetAsync(cudaComputeCounters, 0, sizeof(unsigned long long) * CTR_COUNT, cudaComputeStream));
     CUDA_TRY(cudaEventRecord(cudaComputeEvents[1], cudaComputeStream));
@@ -850,6 +914,16 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
             if (!planFor(passSpp, perRunFixed, args.plan)) return fail(VCRT_ERROR_INVALID_ARGUMENT, "too many work items%s", "");
         }
         done += passSpp;
+        if (usePrimary) {
+            const bool timed = pass < kMaxTimedPasses;
+            if (timed) {
+                while (cudaComputePassEventCount < 2 * (pass + 1)) { CUDA_TRY(cudaEventCreate(&cudaComputePassEvents[cudaComputePassEventCount])); cudaComputePassEventCount++; }
+                CUDA_TRY(cudaEventRecord(cudaComputePassEvents[2 * pass], cudaComputeStream));
+            }
+            rc = fixedMode ? launchPrimaryScan<true>(args, &launches) : launchPrimaryScan<false>(args, &launches);
+            if (rc) return rc;
+            if (timed) { CUDA_TRY(cudaEventRecord(cudaComputePassEvents[2 * pass + 1], cudaComputeStream)); timedPasses = pass + 1; }
+        }
       if (traversal == VCRT_TRAVERSAL_LBVH) {
         const bool stats = (args.flags & kFlagCountStats) != 0;
 #ifdef VCRT_EXPERIMENTS
@@ -937,6 +1011,8 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     CUDA_TRY(cudaEventElapsedTime(&st.renderKernelMs, cudaComputeEvents[1], cudaComputeEvents[2]));
     CUDA_TRY(cudaEventElapsedTime(&st.totalMs, cudaComputeEvents[0], cudaComputeEvents[3]));
     st.kernelLaunches = launches; st.traversalUsed = traversal; st.sampleChunksUsed = chunks;
+    st.primaryRays = ctr[CTR_PRIMARY_RAYS]; st.renderPasses = traces && (traversal == VCRT_TRAVERSAL_BRUTE || traversal == VCRT_TRAVERSAL_LBVH) ? passes : (traces ? 1u : 0u);
+    for (uint32_t i = 0; i < timedPasses; i++) { float ms = 0.f; CUDA_TRY(cudaEventElapsedTime(&ms, cudaComputePassEvents[2 * i], cudaComputePassEvents[2 * i + 1])); st.primaryKernelMs += ms; }
     st.checkFailures = (uint32_t)(ctr[CTR_CHECK_FAILED] > 0xffffffffull ? 0xffffffffull : ctr[CTR_CHECK_FAILED]);
     if (st.badMaterial) return fail(VCRT_ERROR_SCENE, "scene has texture ids outside 1..3 (hits on them were absorbed)%s", "");
     return VCRT_SUCCESS;
@@ -979,16 +1055,19 @@ extern "C" int cudaDestroyRenderer(void) {
     if (cudaComputeDeviceReady) {
         cudaSetDevice(cudaComputeDevice);
         if (cudaComputeStream) cudaStreamSynchronize(cudaComputeStream);
-        void* buffers[] = {cudaComputeSceneBlob, cudaComputeSumPlanes, cudaComputeAccumulated, cudaComputeReduced, cudaComputeFixedSums, cudaComputeFixedReduced,
+        void* buffers[] = {cudaComputePrimary, cudaComputeSceneBlob, cudaComputeSumPlanes, cudaComputeAccumulated, cudaComputeReduced, cudaComputeFixedSums, cudaComputeFixedReduced,
                            cudaComputeResultImage, cudaComputeCounters, cudaComputeWorkCounter, cudaComputeCommScratch, cudaComputeFlushScratch, cudaComputeBvhArena};
         for (void* b : buffers) if (b) cudaFree(b);
         for (int i = 0; i < 16; i++) if (cudaComputeMarkReady[i]) { cudaEventDestroy(cudaComputeMarks[i]); cudaComputeMarkReady[i] = false; }
         for (int i = 0; i < 4; i++) if (cudaComputeEvents[i]) cudaEventDestroy(cudaComputeEvents[i]);
+        for (uint32_t i = 0; i < cudaComputePassEventCount; i++) cudaEventDestroy(cudaComputePassEvents[i]);
+        cudaComputePassEventCount = 0;
         if (cudaComputeStream) cudaStreamDestroy(cudaComputeStream);
     }
     cudaComputeSceneBlob = nullptr; cudaComputeSumPlanes = nullptr; cudaComputeSumPlanesBytes = 0;
     cudaComputeAccumulated = cudaComputeReduced = cudaComputeResultImage = nullptr;
     cudaComputeFixedSums = cudaComputeFixedReduced = nullptr;
+    cudaComputePrimary = nullptr; cudaComputePrimaryCapacity = 0;
     cudaComputeCounters = nullptr; cudaComputeWorkCounter = nullptr; cudaComputeCommScratch = nullptr; cudaComputeFlushScratch = nullptr;
     cudaComputeBvhArena = nullptr; cudaComputeBvhArenaBytes = 0; cudaComputeBvhReady = false;
     if (cudaComputeHostShape) delete[] cudaComputeHostShape;

@@ -117,6 +117,17 @@ struct ItemPlan {
     float invTiles;
 };
 
+// What the primary-visibility kernels (vcrt_kernel_primary.cuh) hand to the path kernels: every sample of a launch after its
+// camera ray and first scatter event.  Two float4 planes; entry of sample s (0-based within the launch) of the pixel with padded
+// tile-order id pid sits at [s * plan.pixelsPadded + pid], so the lanes of a warp read and write consecutive entries.
+//   a = (origin of the scattered ray, state as bits)     state >= 0: device index of the sphere that was hit - the path goes on
+//   b = (direction of the scattered ray, 0)                          with this ray, throughput = that sphere's attenuation, pass 1
+//                                                         state < 0: one of the values below
+struct PrimaryBuffer { float4* a; float4* b; };
+constexpr int kPrimaryEnded = -1;       // the sample ended at its first ray (sky / absorbed / depth 1): b.xyz = its radiance (strict-order sums)
+constexpr int kPrimaryUntraced = -2;    // not pre-traced (a ray outside the tame range, a candidate-list overflow): the path kernel starts at the camera
+constexpr int kPrimaryDone = -3;        // ended AND already added to the fixed-point sums by the primary kernel: nothing left to do
+
 struct RenderArgs {
     Frame frame;
     uint32_t width, height;
@@ -132,10 +143,16 @@ struct RenderArgs {
     uint32_t semantics;       // 0 = the reference shader as it is, 1 = BOOK (vcrt_shade.cuh)
     unsigned long long* counters;  // see Counter enum
     unsigned int* workCounter;     // dynamic item dispenser
+    PrimaryBuffer primary;         // this launch's samples after their first scatter event; a == nullptr: every path starts at the camera
 };
 
+// pixel (px, py) -> its id in 8x4-tile order (the order the primary-visibility kernels write their results in)
+VCRT_DEV uint32_t padded_pixel_id(uint32_t tilesX, uint32_t px, uint32_t py) {
+    return (((py >> 2) * tilesX + (px >> 3)) << 5) | ((py & 3u) << 3) | (px & 7u);
+}
+
 enum Counter { CTR_RAYS = 0, CTR_EXHAUSTED, CTR_BAD_MATERIAL, CTR_CANDIDATES, CTR_OVERFLOWS, CTR_TESTS, CTR_NODES,
-               CTR_HITS0, CTR_HITS1, CTR_HITS2, CTR_HITS3, CTR_PATH0, CTR_CHECK_FAILED = CTR_PATH0 + 8, CTR_COUNT };
+               CTR_HITS0, CTR_HITS1, CTR_HITS2, CTR_HITS3, CTR_PATH0, CTR_CHECK_FAILED = CTR_PATH0 + 8, CTR_PRIMARY_RAYS, CTR_COUNT };
 
 // Bounds checks of our own (compute-sanitizer is closed on the GPU pool): with -DVCRT_CHECKED every hand-computed index into
 // shared, local or global memory is compared with its bound before use and violations are counted (VcrtRenderStats.checkFailures,

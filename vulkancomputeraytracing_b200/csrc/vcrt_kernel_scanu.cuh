@@ -38,7 +38,7 @@
 
 namespace vcrt {
 
-constexpr int kMaxConstSpheres = 3584;                 // 56 KB of the 64 KB constant bank
+constexpr int kMaxConstSpheres = 1792;                 // 28 KB of the 64 KB constant bank (the primary-visibility scan has a table of its own)
 constexpr float kKappaU = 1.52587890625e-05f;          // 2^-16
 __constant__ float4 cSceneHot[kMaxConstSpheres];       // (cx, cy, cz, |c|^2 - R2 rounded down), padded with (0,0,0,+inf)
 
@@ -109,17 +109,6 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
             return true;
         }
     };
-    auto start_sample = [&](int r) {   // shader.comp:46-52
-        uint32_t pixel = ST(SF_PIXEL, r), sample = args.sampleOffset + ST(SF_SAMPLE, r);
-        uint32_t py = pixel / args.width, px = pixel - py * args.width, rnd[4];
-        philox4x32_10(pixel, sample, 0u, 0u, args.seedLo, args.seedHi, rnd);
-        Ray ray = primary_ray(args.frame, px, py, u01(rnd[0]), u01(rnd[1]));
-        ST(SF_OX, r) = __float_as_uint(ray.o.x); ST(SF_OY, r) = __float_as_uint(ray.o.y); ST(SF_OZ, r) = __float_as_uint(ray.o.z);
-        ST(SF_DX, r) = __float_as_uint(ray.d.x); ST(SF_DY, r) = __float_as_uint(ray.d.y); ST(SF_DZ, r) = __float_as_uint(ray.d.z);
-        ST(SF_CR, r) = ST(SF_CG, r) = ST(SF_CB, r) = __float_as_uint(1.0f);
-        ST(SF_PASS, r) = 0u;
-    };
-
     const int scanCount = (int)hdr.scanCount, count = (int)hdr.count;
     const float kPosInf = __int_as_float(0x7f800000);
     uint32_t listCount = 0, exhaustMask = 0;   // candidates of this thread this round; slots that need the exhaustive exact scan
@@ -206,11 +195,14 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
         }
 
         // ---- (3) per slot: exact test of the thread's candidates, shade, and (re)generate.  One copy of every routine.
+        //      A new sample normally comes out of the PrimaryBuffer (vcrt_kernel_primary.cuh) as a scattered ray at pass 1.
         const bool overflow = listCount > (uint32_t)LCAP;
 #pragma unroll 1
         for (int r = 0; r < R; r++) {
-            bool needClaim = firstRound, needStart = false;
-            const uint32_t pixel = firstRound ? kIdle : ST(SF_PIXEL, r);
+            uint32_t pixel = firstRound ? kIdle : ST(SF_PIXEL, r);
+            if (pixel == kIdle && !firstRound) continue;   // the dispenser ran dry while this slot was looking for work
+            bool itemDone = firstRound, useFirst = firstRound, haveResult = false;
+            V3 result = v3(0.f, 0.f, 0.f);   // black: bug B7 (depth exhausted) and absorbed bad materials
             if (pixel != kIdle) {
                 Ray ray; ray.o = v3(STF(SF_OX, r), STF(SF_OY, r), STF(SF_OZ, r)); ray.d = v3(STF(SF_DX, r), STF(SF_DY, r), STF(SF_DZ, r));
                 const float a = vdot(ray.d, ray.d);
@@ -226,7 +218,6 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                     if (VCRT_CHECK(args.counters, j >= 0 && j < count && (exhaustive || e >= nScan || e < LCAP))) hit_exact(sShape[j], j, ray, a, rec, tame);
                 }
                 V3 colour = v3(STF(SF_CR, r), STF(SF_CG, r), STF(SF_CB, r));
-                V3 result = v3(0.f, 0.f, 0.f);   // black: bug B7 (depth exhausted) and absorbed bad materials
                 bool ended = true;
                 if (rec.index < 0) {
                     if (args.flags & kFlagCountStats) atomicAdd(&args.counters[CTR_PATH0 + min(ST(SF_PASS, r), 7u)], 1ull);
@@ -253,7 +244,13 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                         ST(SF_PASS, r) = pass + 1u;
                     }
                 }
-                if (ended) {   // shader.comp:53: color.rgb += ray_color(r), in sample order within the item
+                if (!ended) continue;   // the slot holds a scattered ray: next scan
+                haveResult = true;
+            }
+            // ---- the sample in the slot is finished (or there was none): add it to the sums, take the next one
+            for (;;) {
+                if (haveResult) {   // shader.comp:53: color.rgb += ray_color(r), in sample order within the item
+                    haveResult = false;
                     uint32_t s = ST(SF_SAMPLE, r);
                     const uint32_t s1 = ST(SF_END, r);
                     if (FIXED) {
@@ -267,11 +264,45 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                         if (s < s1) { ST(SF_SUMR, r) = __float_as_uint(sum.x); ST(SF_SUMG, r) = __float_as_uint(sum.y); ST(SF_SUMB, r) = __float_as_uint(sum.z); }
                         else if (VCRT_CHECK(args.counters, chunk < args.chunks && pixel < planeStride)) args.sums[(size_t)chunk * planeStride + pixel] = make_float4(sum.x, sum.y, sum.z, 0.f);   // the item's only global write
                     }
-                    if (s < s1) { ST(SF_SAMPLE, r) = s; needStart = true; } else needClaim = true;
+                    if (s < s1) ST(SF_SAMPLE, r) = s; else itemDone = true;
                 }
+                if (itemDone) {
+                    if (!claim_item(r, (blockIdx.x * R + r) * THREADS + tid, useFirst)) break;   // the dispenser is empty: the slot idles
+                    itemDone = false; useFirst = false;
+                }
+                pixel = ST(SF_PIXEL, r);
+                const uint32_t sLocal = ST(SF_SAMPLE, r);
+                const uint32_t py = pixel / args.width, px = pixel - py * args.width;
+                int state = kPrimaryUntraced;
+                if (args.primary.a) {
+                    const size_t at = (size_t)sLocal * args.plan.pixelsPadded + padded_pixel_id(args.plan.tilesX, px, py);
+                    const float4 ea = __ldcs(args.primary.a + at);
+                    state = __float_as_int(ea.w);
+                    if (state >= 0) {   // the sample goes on after its first scatter event
+                        const float4 eb = __ldcs(args.primary.b + at);
+                        const V3 colour = first_attenuation(sSurf[state], sKind[state], args.semantics);
+                        ST(SF_OX, r) = __float_as_uint(ea.x); ST(SF_OY, r) = __float_as_uint(ea.y); ST(SF_OZ, r) = __float_as_uint(ea.z);
+                        ST(SF_DX, r) = __float_as_uint(eb.x); ST(SF_DY, r) = __float_as_uint(eb.y); ST(SF_DZ, r) = __float_as_uint(eb.z);
+                        ST(SF_CR, r) = __float_as_uint(colour.x); ST(SF_CG, r) = __float_as_uint(colour.y); ST(SF_CB, r) = __float_as_uint(colour.z);
+                        ST(SF_PASS, r) = 1u;
+                        break;
+                    }
+                    if (state == kPrimaryDone) { result = v3(0.f, 0.f, 0.f); haveResult = true; continue; }   // already in the fixed-point sums
+                    if (state == kPrimaryEnded) {
+                        const float4 eb = __ldcs(args.primary.b + at);
+                        result = v3(eb.x, eb.y, eb.z); haveResult = true; continue;
+                    }
+                }
+                // no entry: the sample starts at the camera (shader.comp:46-52) and its primary ray goes through the scan
+                uint32_t rnd[4];
+                philox4x32_10(pixel, args.sampleOffset + sLocal, 0u, 0u, args.seedLo, args.seedHi, rnd);
+                const Ray ray = primary_ray(args.frame, px, py, u01(rnd[0]), u01(rnd[1]));
+                ST(SF_OX, r) = __float_as_uint(ray.o.x); ST(SF_OY, r) = __float_as_uint(ray.o.y); ST(SF_OZ, r) = __float_as_uint(ray.o.z);
+                ST(SF_DX, r) = __float_as_uint(ray.d.x); ST(SF_DY, r) = __float_as_uint(ray.d.y); ST(SF_DZ, r) = __float_as_uint(ray.d.z);
+                ST(SF_CR, r) = ST(SF_CG, r) = ST(SF_CB, r) = __float_as_uint(1.0f);
+                ST(SF_PASS, r) = 0u;
+                break;
             }
-            if (needClaim) needStart = claim_item(r, (blockIdx.x * R + r) * THREADS + tid, firstRound);
-            if (needStart) start_sample(r);
         }
     }
 

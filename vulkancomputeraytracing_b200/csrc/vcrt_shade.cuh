@@ -126,6 +126,18 @@ VCRT_DEV bool scatter(const float4 shape, const float4 surf, int kind, float t, 
     return false;
 }
 
+// Throughput of a path after its FIRST scatter event on a sphere with these material words: what scatter() / scatter_book() make of
+// colour = (1, 1, 1).  The path kernels use it when they take over a sample from the primary-visibility kernels, which hand over
+// the scattered ray and the sphere index but not the colour (same operations, so the same bits: 1 * x is x).
+VCRT_DEV V3 first_attenuation(float4 surf, int kind, uint32_t semantics) {
+    V3 colour = v3(1.f, 1.f, 1.f);
+    if (kind == 1 || kind == 2) {
+        const V3 tint = vmul(colour, v3(surf.x, surf.y, surf.z));
+        colour = (kind == 1 && !semantics) ? vscale(tint, surf.w) : tint;   // bug B4b: the reference's lambertian multiplies by texture.y too
+    }
+    return colour;
+}
+
 // ------------------------------------------------------------------ BOOK semantics (VCRT_SEMANTICS_BOOK)
 // The same path with the reference's matched bugs fixed the way "Ray Tracing in One Weekend" (v4.0.1) writes the routines:
 // face-forwarded normals, uniform-on-the-sphere scatter by rejection sampling, lambertian attenuation = albedo, metal

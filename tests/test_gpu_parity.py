@@ -11,6 +11,7 @@ import ctypes
 import json
 import os
 import subprocess
+import sys
 import zlib
 
 import numpy as np
@@ -488,6 +489,29 @@ def test_uploading_the_same_scene_again_keeps_the_tree_and_the_bits(vcrt):
         assert s5.rays == s6.rays and np.abs(other - simple).max() <= 2.0 ** -22
     finally:
         host.destroy()
+
+
+def test_primary_visibility_pass_changes_no_bit(gpu_scene):
+    # VCRT_TRAVERSAL_BRUTE runs the camera rays and their first scatter event in a kernel of their own (vcrt_kernel_primary.cuh) and
+    # hands the scattered rays to the path kernel.  VCRT_NO_PRIMARY=1 (read once per process) switches that off: a second process
+    # renders the old way, and image bits, ray counts and the statistics counters must agree in both accumulation modes.
+    code = (
+        "import sys, zlib, json; sys.path.insert(0, '.');"
+        "from vulkancomputeraytracing_b200 import cabi, host;"
+        "host.upload_scene(host.generate_scene()); out = [];\n"
+        "for chunks, flags in ((0, 0), (1, 0), (3, cabi.VCRT_FLAG_COUNT_STATS)):\n"
+        "    img, st = host.render(203, 113, 5, depth=9, traversal=1, sample_chunks=chunks, flags=flags)\n"
+        "    out.append([zlib.crc32(img.tobytes()), st.rays, st.depthExhausted, list(st.hitsByMaterial), list(st.pathLength), st.primaryRays])\n"
+        "print(json.dumps(out))")
+    env = dict(os.environ, VCRT_NO_PRIMARY="1")
+    other = json.loads(subprocess.run([sys.executable, "-c", code], cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))), env=env,
+                                      capture_output=True, text=True, check=True).stdout.strip().splitlines()[-1])
+    for (chunks, flags), want in zip(((0, 0), (1, 0), (3, cabi.VCRT_FLAG_COUNT_STATS)), other):
+        img, st = host.render(203, 113, 5, depth=9, traversal=BRUTE, sample_chunks=chunks, flags=flags)
+        got = [zlib.crc32(img.tobytes()), st.rays, st.depthExhausted, list(st.hitsByMaterial), list(st.pathLength)]
+        assert got == want[:5], (chunks, flags)
+        assert st.primaryRays == 203 * 113 * 5 and want[5] == 0      # every camera ray went through the primary kernel here, none there
+        assert st.primaryKernelMs > 0 and st.renderPasses == 1
 
 
 def test_schlick_dense(vcrt):

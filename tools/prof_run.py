@@ -11,6 +11,6 @@ for i in range(reps):
     _, st = host.render(W, H, spp, traversal=trav, sample_chunks=chunks, download=False, shape=shape)
     print(f'{W}x{H}x{spp} trav={st.traversalUsed} n={n}: kernel {st.renderKernelMs:.2f} ms total {st.totalMs:.2f} ms  {st.samples/st.renderKernelMs/1e3:.1f} Msamples/s  '
           f'{st.rays/st.renderKernelMs/1e3:.1f} Mrays/s  {st.rays*n/st.renderKernelMs/1e9:.3f} Ttests/s  alg {st.rays*n*17/st.renderKernelMs/1e9:.1f} TF  '
-          f'rays/sample {st.rays/st.samples:.4f} cand/ray {st.candidates/max(1,st.rays):.2f} ovf {st.listOverflows} nodes/ray {st.nodeVisits/max(1,st.rays):.1f}', flush=True)
+          f'primary {st.primaryKernelMs:.2f} ms  rays/sample {st.rays/st.samples:.4f} cand/ray {st.candidates/max(1,st.rays):.2f} ovf {st.listOverflows} nodes/ray {st.nodeVisits/max(1,st.rays):.1f}', flush=True)
 tf, mhz = host.fp32_peak(); print(f'fp32 peak {tf:.1f} TF at {mhz:.0f} MHz')
 host.destroy()

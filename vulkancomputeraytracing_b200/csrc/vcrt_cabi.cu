@@ -885,6 +885,17 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     args.chunks = chunks; args.flags = p->flags; args.sums = cudaComputeSumPlanes;
     args.fixedSums = cudaComputeFixedSums; args.plan = plan;
     args.counters = cudaComputeCounters; args.workCounter = cudaComputeWorkCounter;
+    // a thread of the primary kernel traces kPrimaryRays rays: S samples x kPrimaryRays / S tiles, S the power of two that leaves
+    // the fewest sample slots empty over the launch (the larger one on a tie: the rays of one pixel share their candidates)
+    args.primarySamples = 1u;
+    {
+        const uint32_t sppMax = fixedMode ? (p->samplesPerPixel + passes - 1u) / passes : p->samplesPerPixel;
+        uint32_t bestWaste = 0xffffffffu;
+        for (uint32_t sPer = (uint32_t)kPrimaryRays; sPer >= 1u; sPer >>= 1) {
+            const uint32_t waste = (sppMax + sPer - 1u) / sPer * sPer - sppMax;
+            if (waste < bestWaste) { bestWaste = waste; args.primarySamples = sPer; }
+        }
+    }
     args.primary.a = usePrimary ? cudaComputePrimary : nullptr;
     args.primary.b = usePrimary ? cudaComputePrimary + cudaComputePrimaryCapacity : nullptr;
 

@@ -144,6 +144,7 @@ struct RenderArgs {
     unsigned long long* counters;  // see Counter enum
     unsigned int* workCounter;     // dynamic item dispenser
     PrimaryBuffer primary;         // this launch's samples after their first scatter event; a == nullptr: every path starts at the camera
+    uint32_t primarySamples;       // primary-visibility kernel: a thread's rays are this many samples (1, 2, 4, ...) of rays / this many neighbouring tiles
 };
 
 // pixel (px, py) -> its id in 8x4-tile order (the order the primary-visibility kernels write their results in)

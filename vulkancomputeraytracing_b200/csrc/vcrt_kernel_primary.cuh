@@ -46,7 +46,11 @@ namespace vcrt {
 __constant__ float4 cPrimaryHot[kMaxConstSpheres];     // (c'x, c'y, c'z, |c'|^2 - R2 rounded down), c' = centre - camera; padding (0,0,0,+inf)
 
 constexpr int kPrimaryThreads = 256;
-constexpr int kPrimaryRays = 4;                        // samples of one pixel per thread
+#ifndef VCRT_PRIMARY_RAYS
+#define VCRT_PRIMARY_RAYS 4
+#endif
+constexpr int kPrimaryRays = VCRT_PRIMARY_RAYS;        // samples of one pixel per thread (even)
+constexpr int kPrimaryPairs = kPrimaryRays / 2;
 constexpr int kPrimaryListCap = 40;
 
 __host__ __device__ inline size_t primary_scan_smem(uint32_t blobBytes) { return 16 + (size_t)blobBytes + (size_t)kPrimaryListCap * kPrimaryThreads * 2; }
@@ -85,7 +89,9 @@ VCRT_DEV void primary_finish(const RenderArgs& args, uint32_t pixel, uint32_t sa
     if (!ended || !FIXED) __stcs(args.primary.b + at, b);
 }
 
-// One warp = one 8x4 pixel tile x 4 consecutive samples; lane = pixel.
+// One warp = kPrimaryRays rays per lane: S consecutive samples (args.primarySamples, a power of two chosen by the host so that few
+// sample slots stay empty: 4 at 500 spp, 1 at the reference's default of 1 spp) of the lane's pixel in kPrimaryRays / S neighbouring
+// 8x4 pixel tiles.
 template <bool FIXED>
 __global__ void __launch_bounds__(kPrimaryThreads, 3) primary_scan_kernel(const unsigned char* __restrict__ blobGlobal, RenderArgs args, int scanPad) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -105,8 +111,10 @@ __global__ void __launch_bounds__(kPrimaryThreads, 3) primary_scan_kernel(const 
     unsigned short* sList = reinterpret_cast<unsigned short*>(blob + blobBytes);
 #define PLIST(e) sList[(e) * kPrimaryThreads + tid]
     const int scanCount = (int)hdr.scanCount, count = (int)hdr.count;
-    const uint32_t tiles = args.plan.tiles, groups = (args.spp + kPrimaryRays - 1u) / kPrimaryRays;
-    const uint32_t units = tiles * groups;   // the host keeps tiles x samples per launch below 2^31
+    const uint32_t tiles = args.plan.tiles;
+    const uint32_t sPer = args.primarySamples, sShift = 31u - __clz(sPer), tPer = (uint32_t)kPrimaryRays >> sShift;
+    const uint32_t tileGroups = (tiles + tPer - 1u) / tPer, sampleGroups = (args.spp + sPer - 1u) >> sShift;
+    const uint32_t units = tileGroups * sampleGroups;   // the host keeps tiles x samples per launch below 2^31
     const uint32_t warpsPerGrid = gridDim.x * (kPrimaryThreads / 32);
     // the trip count depends on nothing but the launch, so the scan below sits in warp-uniform control flow: that is what lets
     // ptxas feed the sphere operands through uniform registers (LDCU -> UR.F32) instead of LDC into the register file
@@ -118,18 +126,22 @@ __global__ void __launch_bounds__(kPrimaryThreads, 3) primary_scan_kernel(const 
 #pragma unroll 1
     for (uint32_t trip = 0; trip < trips; trip++) {
         const uint32_t unit = trip * warpsPerGrid + blockIdx.x * (kPrimaryThreads / 32) + (tid >> 5);
-        const uint32_t group = unit / tiles, tile = unit - group * tiles;
-        const uint32_t ty = tile / args.plan.tilesX, tx = tile - ty * args.plan.tilesX;
-        const uint32_t px = tx * 8u + (lane & 7u), py = ty * 4u + (lane >> 3);
-        const bool inside = unit < units && px < args.width && py < args.height;
-        const uint32_t pixel = py * args.width + px;
-        // the four camera rays (shader.comp:46-52) and their unit directions
+        const uint32_t sampleGroup = unit / tileGroups, tileGroup = unit - sampleGroup * tileGroups;
+        // ray k of the thread: sample (k mod S) of the group, tile (k / S) of the group
+        auto ray_slot = [&](int k, uint32_t& tile, uint32_t& s, uint32_t& px, uint32_t& py) -> bool {
+            tile = tileGroup * tPer + ((uint32_t)k >> sShift); s = (sampleGroup << sShift) + ((uint32_t)k & (sPer - 1u));
+            const uint32_t ty = tile / args.plan.tilesX, tx = tile - ty * args.plan.tilesX;
+            px = tx * 8u + (lane & 7u); py = ty * 4u + (lane >> 3);
+            return unit < units && tile < tiles && s < args.spp && px < args.width && py < args.height;
+        };
+        // the camera rays (shader.comp:46-52) and their unit directions
         V3 d[kPrimaryRays]; float dh[kPrimaryRays][3]; uint32_t okMask = 0u;
 #pragma unroll
         for (int k = 0; k < kPrimaryRays; k++) {
-            const uint32_t s = group * kPrimaryRays + k;
+            uint32_t tile, s, px, py;
             dh[k][0] = dh[k][1] = dh[k][2] = 0.f; d[k] = v3(0.f, 0.f, 0.f);
-            if (inside && s < args.spp) {
+            if (ray_slot(k, tile, s, px, py)) {
+                const uint32_t pixel = py * args.width + px;
                 uint32_t rnd[4];
                 philox4x32_10(pixel, args.sampleOffset + s, 0u, 0u, args.seedLo, args.seedHi, rnd);
                 const Ray ray = primary_ray(args.frame, px, py, u01(rnd[0]), u01(rnd[1]));
@@ -142,9 +154,10 @@ __global__ void __launch_bounds__(kPrimaryThreads, 3) primary_scan_kernel(const 
                 }
             }
         }
-        const u64 dx0 = pack2(dh[0][0], dh[1][0]), dy0 = pack2(dh[0][1], dh[1][1]), dz0 = pack2(dh[0][2], dh[1][2]);
-        const u64 dx1 = pack2(dh[2][0], dh[3][0]), dy1 = pack2(dh[2][1], dh[3][1]), dz1 = pack2(dh[2][2], dh[3][2]);
-        // the scan: per sphere two LDCU.64, 8 packed FP32 operations for four rays, a max and one compare
+        u64 dxp[kPrimaryPairs], dyp[kPrimaryPairs], dzp[kPrimaryPairs];
+#pragma unroll
+        for (int p = 0; p < kPrimaryPairs; p++) { dxp[p] = pack2(dh[2 * p][0], dh[2 * p + 1][0]); dyp[p] = pack2(dh[2 * p][1], dh[2 * p + 1][1]); dzp[p] = pack2(dh[2 * p][2], dh[2 * p + 1][2]); }
+        // the scan: per sphere two LDCU.64, 4 packed FP32 operations per ray pair, a max over the thread's rays and one compare
         uint32_t listCount = 0u;
         auto scan_block = [&]<int U>(int at) -> uint32_t {
             uint32_t mEven = 0u, mOdd = 0u;
@@ -153,11 +166,15 @@ __global__ void __launch_bounds__(kPrimaryThreads, 3) primary_scan_kernel(const 
                 (void)VCRT_CHECK(args.counters, at + u < scanPad && at + u < kMaxConstSpheres);
                 const float4 s = cPrimaryHot[at + u];
                 const u64 cx = pack2(s.x, s.x), cy = pack2(s.y, s.y), cz = pack2(s.z, s.z);
-                u64 t0 = fmul2(cz, dz0); t0 = ffma2(cy, dy0, t0); t0 = ffma2(cx, dx0, t0);
-                u64 t1 = fmul2(cz, dz1); t1 = ffma2(cy, dy1, t1); t1 = ffma2(cx, dx1, t1);
-                const u64 q0 = fmul2(t0, t0), q1 = fmul2(t1, t1);
-                float a0, a1, a2, a3; unpack2(q0, a0, a1); unpack2(q1, a2, a3);
-                flag_if_ge(u & 1 ? mOdd : mEven, fmaxf(fmaxf(a0, a1), fmaxf(a2, a3)), s.w, 1u << u);
+                float qmax = -__int_as_float(0x7f800000);
+#pragma unroll
+                for (int p = 0; p < kPrimaryPairs; p++) {
+                    u64 t = fmul2(cz, dzp[p]); t = ffma2(cy, dyp[p], t); t = ffma2(cx, dxp[p], t);
+                    const u64 q = fmul2(t, t);
+                    float q0, q1; unpack2(q, q0, q1);
+                    qmax = fmaxf(qmax, fmaxf(q0, q1));
+                }
+                flag_if_ge(u & 1 ? mOdd : mEven, qmax, s.w, 1u << u);
             }
             return mEven | mOdd;
         };
@@ -183,8 +200,9 @@ __global__ void __launch_bounds__(kPrimaryThreads, 3) primary_scan_kernel(const 
         const bool overflow = listCount > (uint32_t)kPrimaryListCap;
 #pragma unroll 1
         for (int k = 0; k < kPrimaryRays; k++) {
-            const uint32_t s = group * kPrimaryRays + k;
-            if (!(inside && s < args.spp)) continue;
+            uint32_t tile, s, px, py;
+            if (!ray_slot(k, tile, s, px, py)) continue;
+            const uint32_t pixel = py * args.width + px;
             const size_t at = (size_t)s * args.plan.pixelsPadded + ((size_t)tile << 5) + lane;
             if (overflow || !((okMask >> k) & 1u)) { __stcs(args.primary.a + at, make_float4(0.f, 0.f, 0.f, __int_as_float(kPrimaryUntraced))); continue; }
             Ray ray; ray.o = origin; ray.d = d[k];

@@ -339,6 +339,14 @@ def roofline(b, leg, name):
                                      "frac": p_rays * n * FLOP_PER_TEST / p_s * 1e-12 / peak,
                                      "frac_executed": p_rays * n * FLOP_PER_PRIMARY_FILTER / p_s * 1e-12 / peak,
                                      "executed": f"{FLOP_PER_PRIMARY_FILTER} flop per (camera ray, sphere): the camera-relative filter"}
+        try:   # the primary kernel's DRAM traffic and pipe figures from the same committed capture
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                t = json.load(f).get(PRIMARY_KERNEL, {}).get(name)
+            if t and "primary_kernel" in out:
+                out["primary_kernel"].update({"traffic": t["dram_bytes_per_launch"], "ncu_fma_pipe_active_pct": t.get("fma_pipe_active_pct"),
+                                              "ncu_issue_active_pct": t.get("issue_active_pct"), "ncu_threads_per_instruction": t.get("threads_per_instruction")})
+        except (OSError, ValueError):
+            pass
         out["step"] = {"kernels": [PRIMARY_KERNEL, leg["kernel"]] if p_rays else [leg["kernel"]], "kernel_ms_per_step": kernel_s * 1e3 / leg["steps"],
                        "achieved": raw["rays"] * n * FLOP_PER_TEST / kernel_s * 1e-12, "frac": raw["rays"] * n * FLOP_PER_TEST / kernel_s * 1e-12 / peak,
                        "note": "all rays of the step x spheres x 17 flop over the time of both kernels: the algorithmic rate of the brute-force path as a whole"}

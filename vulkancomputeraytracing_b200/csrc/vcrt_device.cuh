@@ -35,6 +35,14 @@ __device__ __noinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
 __device__ __noinline__ float fsqrt(float a) { return __fsqrt_rn(a); }
 #endif
 
+typedef unsigned long long u64;
+
+// ------------------------------------------------------------------ packed f32x2 (sm_100a FFMA2)
+VCRT_DEV u64 pack2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+VCRT_DEV void unpack2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+VCRT_DEV u64 fmul2(u64 a, u64 b) { u64 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+VCRT_DEV u64 ffma2(u64 a, u64 b, u64 c) { u64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
 struct V3 { float x, y, z; };
 VCRT_DEV V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
 VCRT_DEV V3 vadd(V3 a, V3 b) { return v3(fadd(a.x, b.x), fadd(a.y, b.y), fadd(a.z, b.z)); }

@@ -170,6 +170,8 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
     uint32_t first = octant * (scene.treeCount - 1u);   // 8 (count - 1) < 2^32: the ABI caps a scene far below that
     asm volatile("" : "+r"(first));                      // keep it in a register: recomputing it per visit costs 8 instructions
     const BvhNode* nodes = scene.octNodes;
+    const u64 ix2 = pack2(ix, ix), iy2 = pack2(iy, iy), iz2 = pack2(iz, iz);
+    const u64 bnx2 = pack2(bnx, bnx), bny2 = pack2(bny, bny), bnz2 = pack2(bnz, bnz), bfx2 = pack2(bfx, bfx), bfy2 = pack2(bfy, bfy), bfz2 = pack2(bfz, bfz);
     int sp = 0, node = 0;
     for (;;) {
         if (node >= 0) {
@@ -177,11 +179,14 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
             if (!VCRT_CHECK(n.counters, (uint32_t)node < scene.treeCount - 1u)) break;
             const float4 na = __ldg(&nodes[first + (uint32_t)node].a), nb = __ldg(&nodes[first + (uint32_t)node].b), nc = __ldg(&nodes[first + (uint32_t)node].c);
             const int2 ch = __ldg(reinterpret_cast<const int2*>(&nodes[first + (uint32_t)node].child0));
-            // child0: near (na.x, na.y, na.z) far (na.w, nb.x, nb.y); child1: near (nb.z, nb.w, nc.x) far (nc.y, nc.z, nc.w)
-            const float n0 = fmaxf(fmaxf(fmaf(na.x, ix, bnx), fmaf(na.y, iy, bny)), fmaf(na.z, iz, bnz));
-            const float f0 = fminf(fminf(fmaf(na.w, ix, bfx), fmaf(nb.x, iy, bfy)), fmaf(nb.y, iz, bfz));
-            const float n1 = fmaxf(fmaxf(fmaf(nb.z, ix, bnx), fmaf(nb.w, iy, bny)), fmaf(nc.x, iz, bnz));
-            const float f1 = fminf(fminf(fmaf(nc.y, ix, bfx), fmaf(nc.z, iy, bfy)), fmaf(nc.w, iz, bfz));
+            // both children per packed FMA: na = (near0.x, near1.x, near0.y, near1.y), nb = (near0.z, near1.z, far0.x, far1.x),
+            // nc = (far0.y, far1.y, far0.z, far1.z)
+            float nx0, nx1, ny0, ny1, nz0, nz1, fx0, fx1, fy0, fy1, fz0, fz1;
+            unpack2(ffma2(pack2(na.x, na.y), ix2, bnx2), nx0, nx1); unpack2(ffma2(pack2(na.z, na.w), iy2, bny2), ny0, ny1);
+            unpack2(ffma2(pack2(nb.x, nb.y), iz2, bnz2), nz0, nz1); unpack2(ffma2(pack2(nb.z, nb.w), ix2, bfx2), fx0, fx1);
+            unpack2(ffma2(pack2(nc.x, nc.y), iy2, bfy2), fy0, fy1); unpack2(ffma2(pack2(nc.z, nc.w), iz2, bfz2), fz0, fz1);
+            const float n0 = fmaxf(fmaxf(nx0, ny0), nz0), f0 = fminf(fminf(fx0, fy0), fz0);
+            const float n1 = fmaxf(fmaxf(nx1, ny1), nz1), f1 = fminf(fminf(fx1, fy1), fz1);
             const bool h0 = !(n0 > f0) && !(f0 < 0.f) && !(n0 > rec.t);   // written so that a NaN bound passes
             const bool h1 = !(n1 > f1) && !(f1 < 0.f) && !(n1 > rec.t);
             if (h0 && h1) {

@@ -29,14 +29,6 @@
 
 namespace vcrt {
 
-typedef unsigned long long u64;
-
-// ------------------------------------------------------------------ packed f32x2 (sm_100a FFMA2)
-VCRT_DEV u64 pack2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
-VCRT_DEV void unpack2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-VCRT_DEV u64 fmul2(u64 a, u64 b) { u64 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
-VCRT_DEV u64 ffma2(u64 a, u64 b, u64 c) { u64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
-
 // ------------------------------------------------------------------ TMA bulk copy + mbarrier
 VCRT_DEV uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 VCRT_DEV void mbar_init(uint64_t* bar, uint32_t count) {

@@ -46,6 +46,9 @@ namespace vcrt {
 __constant__ float4 cPrimaryHot[kMaxConstSpheres];     // (c'x, c'y, c'z, |c'|^2 - R2 rounded down), c' = centre - camera; padding (0,0,0,+inf)
 
 constexpr int kPrimaryThreads = 256;
+#ifndef VCRT_PRIMARY_CTAS
+#define VCRT_PRIMARY_CTAS 3      // resident CTAs per SM the register budget is set for (85 registers); 4 (64 registers, 20 bytes of spills) measured 8 % slower
+#endif
 #ifndef VCRT_PRIMARY_RAYS
 #define VCRT_PRIMARY_RAYS 4
 #endif
@@ -93,7 +96,7 @@ VCRT_DEV void primary_finish(const RenderArgs& args, uint32_t pixel, uint32_t sa
 // sample slots stay empty: 4 at 500 spp, 1 at the reference's default of 1 spp) of the lane's pixel in kPrimaryRays / S neighbouring
 // 8x4 pixel tiles.
 template <bool FIXED>
-__global__ void __launch_bounds__(kPrimaryThreads, 3) primary_scan_kernel(const unsigned char* __restrict__ blobGlobal, RenderArgs args, int scanPad) {
+__global__ void __launch_bounds__(kPrimaryThreads, VCRT_PRIMARY_CTAS) primary_scan_kernel(const unsigned char* __restrict__ blobGlobal, RenderArgs args, int scanPad) {
     extern __shared__ __align__(16) unsigned char smem[];
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
     unsigned char* blob = smem + 16;

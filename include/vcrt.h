@@ -61,7 +61,7 @@ typedef struct VcrtCamera {
 
 /* How rays find their nearest sphere. */
 enum {
-    VCRT_TRAVERSAL_AUTO = 0,    /* the fastest for the scene: LBVH from a few dozen spheres on, brute force below */
+    VCRT_TRAVERSAL_AUTO = 0,    /* the fastest for the scene: the GPU-built LBVH (measured faster than the scan at every size) */
     VCRT_TRAVERSAL_BRUTE = 1,   /* every ray tests every sphere (what the reference does, functions.glsl:77-81) */
     VCRT_TRAVERSAL_LBVH = 2,    /* GPU-built linear BVH */
     VCRT_TRAVERSAL_SIMPLE = 3   /* one thread per pixel, reference statement order; the on-device cross-check */

@@ -744,7 +744,7 @@ static bool scanUFits(int threads, int pairs, int lcap) {
 }
 
 static const size_t kSmemBudget = 227 * 1024;
-static const uint32_t kBruteForceLimit = 6;   // spheres; above this VCRT_TRAVERSAL_AUTO takes the LBVH (measured faster from 8 spheres up)
+static const uint32_t kPrimaryMinSpheres = 32;   // the primary-visibility pass pays from ~40 scan spheres on (8: 9.4 ms with, 7.4 ms without; 40: 9.8 / 9.9; 485: 38.8 / 46.0 at 1080p x 64 spp)
 static bool scanFits(int threads, int pairs, int cap) {
     size_t state = (size_t)SF_COUNT * 2 * pairs * threads * 4, lists = (size_t)(cap + 2) * 2 * pairs * threads * 2;
     return 16 + (size_t)cudaComputeSceneHeader.bytes + state + lists <= kSmemBudget && cudaComputeSceneHeader.scanPad < 65536u;
@@ -764,10 +764,10 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     if (!cudaComputeSceneReady) return fail(VCRT_ERROR_NOT_READY, "cudaRender before cudaUploadScene%s", "");
 
     uint32_t traversal = p->traversal;
-    // AUTO = the fastest: the LBVH beats the brute-force scan from 8 spheres on (1.05x at 8, 1.5x at 100, 2.9x at 485 spheres,
-    // DESIGN.md section 6); only a handful of spheres leaves the tree nothing to prune
-    if (traversal == VCRT_TRAVERSAL_AUTO)
-        traversal = (cudaComputeSceneHeader.count <= kBruteForceLimit && (scanUFits(1024, 1, 30) || scanFits(256, 2, 12))) ? VCRT_TRAVERSAL_BRUTE : VCRT_TRAVERSAL_LBVH;
+    // AUTO = the fastest, and that is the LBVH kernel at every scene size (tools/crossover.py, 1080p x 64 spp, LBVH / brute:
+    // 2 spheres 4.5 / 7.4 ms, 8: 6.4 / 7.4, 40: 7.2 / 9.8, 100: 9.0 / 13.9, 485: 14.6 / 38.8): with nothing in the tree it is a
+    // path tracer over the few spheres it tests directly, without the scan kernel's slot machinery
+    if (traversal == VCRT_TRAVERSAL_AUTO) traversal = VCRT_TRAVERSAL_LBVH;
     // A NaN centre or radius makes hit_sphere accept the sphere with t = NaN (every comparison of functions.glsl:20-31 is false),
     // after which the reference's result depends on the ORDER of the scan; an infinite one poisons the filter / the boxes.
     // Such scenes are rendered by the in-order exhaustive kernel, whatever was asked for.
@@ -830,7 +830,7 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     // in the environment switches it off (A/B measurements); the first-generation brute-force kernel (scenes beyond ~1200
     // spheres) does not use it, and for the LBVH it was measured to lose.
     static const bool primaryDisabled = getenv("VCRT_NO_PRIMARY") && atoi(getenv("VCRT_NO_PRIMARY")) != 0;
-    bool usePrimary = traces && !primaryDisabled && traversal == VCRT_TRAVERSAL_BRUTE && scanUFits(512, 2, 30) &&
+    bool usePrimary = traces && !primaryDisabled && traversal == VCRT_TRAVERSAL_BRUTE && scanUFits(512, 2, 30) && cudaComputeSceneHeader.scanCount >= kPrimaryMinSpheres &&
                       primary_scan_smem(cudaComputeSceneHeader.bytes) <= kSmemBudget;
 #ifdef VCRT_EXPERIMENTS
     if (p->reserved[1] != 0 && p->reserved[1] != 10 && p->reserved[1] != 12) usePrimary = false;   // only the product kernels read the buffer

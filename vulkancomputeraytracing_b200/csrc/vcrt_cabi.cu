@@ -898,6 +898,7 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     }
     args.primary.a = usePrimary ? cudaComputePrimary : nullptr;
     args.primary.b = usePrimary ? cudaComputePrimary + cudaComputePrimaryCapacity : nullptr;
+    args.primary.entries = usePrimary ? cudaComputePrimaryCapacity : 0;
 
     uint32_t launches = 0, timedPasses = 0;
     CUDA_TRY(cudaEventRecord(cudaComputeEvents[0], cudaComputeStream));

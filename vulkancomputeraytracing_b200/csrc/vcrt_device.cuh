@@ -131,7 +131,7 @@ struct ItemPlan {
 //   a = (origin of the scattered ray, state as bits)     state >= 0: device index of the sphere that was hit - the path goes on
 //   b = (direction of the scattered ray, 0)                          with this ray, throughput = that sphere's attenuation, pass 1
 //                                                         state < 0: one of the values below
-struct PrimaryBuffer { float4* a; float4* b; };
+struct PrimaryBuffer { float4* a; float4* b; size_t entries; };   // entries: capacity of each plane (checked build)
 constexpr int kPrimaryEnded = -1;       // the sample ended at its first ray (sky / absorbed / depth 1): b.xyz = its radiance (strict-order sums)
 constexpr int kPrimaryUntraced = -2;    // not pre-traced (a ray outside the tame range, a candidate-list overflow): the path kernel starts at the camera
 constexpr int kPrimaryDone = -3;        // ended AND already added to the fixed-point sums by the primary kernel: nothing left to do

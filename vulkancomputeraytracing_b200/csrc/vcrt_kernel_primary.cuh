@@ -207,6 +207,7 @@ __global__ void __launch_bounds__(kPrimaryThreads, VCRT_PRIMARY_CTAS) primary_sc
             if (!ray_slot(k, tile, s, px, py)) continue;
             const uint32_t pixel = py * args.width + px;
             const size_t at = (size_t)s * args.plan.pixelsPadded + ((size_t)tile << 5) + lane;
+            if (!VCRT_CHECK(args.counters, at < args.primary.entries)) continue;
             if (overflow || !((okMask >> k) & 1u)) { __stcs(args.primary.a + at, make_float4(0.f, 0.f, 0.f, __int_as_float(kPrimaryUntraced))); continue; }
             Ray ray; ray.o = origin; ray.d = d[k];
             const float a = vdot(ray.d, ray.d);

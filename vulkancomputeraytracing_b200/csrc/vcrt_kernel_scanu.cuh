@@ -276,6 +276,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                 int state = kPrimaryUntraced;
                 if (args.primary.a) {
                     const size_t at = (size_t)sLocal * args.plan.pixelsPadded + padded_pixel_id(args.plan.tilesX, px, py);
+                    (void)VCRT_CHECK(args.counters, at < args.primary.entries);
                     const float4 ea = __ldcs(args.primary.a + at);
                     state = __float_as_int(ea.w);
                     if (state >= 0) {   // the sample goes on after its first scatter event

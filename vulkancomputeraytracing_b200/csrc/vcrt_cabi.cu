@@ -659,11 +659,12 @@ static int ensureBvh(void) {
 template <bool FIXED>
 static int launchPrimaryScan(const RenderArgs& args, uint32_t* launches) {
     const size_t smem = primary_scan_smem(cudaComputeSceneHeader.bytes);
-    CUDA_TRY(cudaFuncSetAttribute(primary_scan_kernel<FIXED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    auto kernel = args.semantics ? primary_scan_kernel<FIXED, true> : primary_scan_kernel<FIXED, false>;
+    CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int perSm = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, primary_scan_kernel<FIXED>, kPrimaryThreads, smem));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, kPrimaryThreads, smem));
     if (perSm < 1) perSm = 1;
-    primary_scan_kernel<FIXED><<<(unsigned int)(cudaComputeSmCount * perSm), kPrimaryThreads, smem, cudaComputeStream>>>(cudaComputeSceneBlob, args, (int)cudaComputeSceneHeader.scanPad);
+    kernel<<<(unsigned int)(cudaComputeSmCount * perSm), kPrimaryThreads, smem, cudaComputeStream>>>(cudaComputeSceneBlob, args, (int)cudaComputeSceneHeader.scanPad);
     CUDA_TRY(cudaGetLastError());
     *launches += 1;
     return VCRT_SUCCESS;
@@ -672,10 +673,10 @@ static int launchPrimaryScan(const RenderArgs& args, uint32_t* launches) {
 template <bool FIXED, bool STATS, bool FLAT>
 static int launchLbvh(const RenderArgs& args, uint32_t* launches) {
 #ifdef VCRT_EXPERIMENTS
-    auto kernel = FLAT ? render_lbvh_flat_kernel<FIXED, STATS> : render_lbvh_kernel<FIXED, STATS>;
+    auto kernel = FLAT ? (args.semantics ? render_lbvh_flat_kernel<FIXED, STATS, true> : render_lbvh_flat_kernel<FIXED, STATS, false>) : render_lbvh_kernel<FIXED, STATS>;
 #else
     static_assert(FLAT, "the first-generation LBVH kernel is an experiment (tools/experiments)");
-    auto kernel = render_lbvh_flat_kernel<FIXED, STATS>;
+    auto kernel = args.semantics ? render_lbvh_flat_kernel<FIXED, STATS, true> : render_lbvh_flat_kernel<FIXED, STATS, false>;
 #endif
     int perSm = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, 256, 0));
@@ -708,7 +709,7 @@ template <int THREADS, int PAIRS, int LCAP, bool FIXED>
 static int launchScanU(const RenderArgs& args, uint32_t* launches) {
     using Cfg = ScanUConfig<THREADS, PAIRS, LCAP>;
     const size_t smem = Cfg::smem_bytes(cudaComputeSceneHeader.bytes);
-    auto kernel = render_scanu_kernel<THREADS, PAIRS, LCAP, FIXED>;
+    auto kernel = args.semantics ? render_scanu_kernel<THREADS, PAIRS, LCAP, FIXED, true> : render_scanu_kernel<THREADS, PAIRS, LCAP, FIXED, false>;
     CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const unsigned int grid = (unsigned int)cudaComputeSmCount;   // persistent: one CTA per SM
     const unsigned int firstDynamicItem = grid * Cfg::R * THREADS;

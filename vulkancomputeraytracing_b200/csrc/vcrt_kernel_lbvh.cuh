@@ -207,7 +207,7 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
     }
 }
 
-template <bool FIXED, bool STATS>
+template <bool FIXED, bool STATS, bool BOOK = false>   // BOOK: VCRT_SEMANTICS_BOOK as a compile-time variant (see render_scanu_kernel)
 __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhScene scene, RenderArgs args) {
     const uint32_t pixels = args.width * args.height;
     const uint32_t sppPerChunk = args.plan.sppPerRun;   // host-made plan (vcrt_device.cuh)
@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhS
             philox4x32_10(pixel, sample, pass + 1u, 0u, args.seedLo, args.seedHi, rnd);
             float u[4] = {u01(rnd[0]), u01(rnd[1]), u01(rnd[2]), u01(rnd[3])};
             int outcome;   // 0 = unknown material, 1 = scattered, 2 = absorbed by the material (BOOK metal)
-            if (args.semantics) {
+            if (BOOK) {
                 BookDraws g; g.pixel = pixel; g.sample = sample; g.event = pass + 1u; g.seedLo = args.seedLo; g.seedHi = args.seedHi;
                 outcome = scatter_book(__ldg(&scene.shape[rec.device]), __ldg(&scene.surf[rec.device]), __ldg(&scene.kind[rec.device]), rec.t, ray, colour, u, g);
             } else outcome = scatter(__ldg(&scene.shape[rec.device]), __ldg(&scene.surf[rec.device]), __ldg(&scene.kind[rec.device]), rec.t, ray, colour, u) ? 1 : 0;

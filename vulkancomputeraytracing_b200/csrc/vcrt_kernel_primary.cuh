@@ -61,7 +61,7 @@ __host__ __device__ inline size_t primary_scan_smem(uint32_t blobBytes) { return
 struct PrimaryCounts { uint32_t rays, exhausted, bad; };
 
 // The first scatter event of one sample (functions.glsl:82-90 for pass 0) and its hand-over.  index < 0: the camera ray left the scene.
-template <bool FIXED>
+template <bool FIXED, bool BOOK>
 VCRT_DEV void primary_finish(const RenderArgs& args, uint32_t pixel, uint32_t sampleGlobal, size_t at, Ray ray, float t, int index,
                              float4 shape, float4 surf, int kind, PrimaryCounts& n) {
     V3 colour = v3(1.f, 1.f, 1.f), result = v3(0.f, 0.f, 0.f);   // black: bug B7 (depth exhausted) and absorbed bad materials
@@ -75,7 +75,7 @@ VCRT_DEV void primary_finish(const RenderArgs& args, uint32_t pixel, uint32_t sa
         philox4x32_10(pixel, sampleGlobal, 1u, 0u, args.seedLo, args.seedHi, rnd);
         float u[4] = {u01(rnd[0]), u01(rnd[1]), u01(rnd[2]), u01(rnd[3])};
         int outcome;   // 0 = unknown material, 1 = scattered, 2 = absorbed by the material (BOOK metal)
-        if (args.semantics) {
+        if (BOOK) {
             BookDraws g; g.pixel = pixel; g.sample = sampleGlobal; g.event = 1u; g.seedLo = args.seedLo; g.seedHi = args.seedHi;
             outcome = scatter_book(shape, surf, kind, t, ray, colour, u, g);
         } else outcome = scatter(shape, surf, kind, t, ray, colour, u) ? 1 : 0;
@@ -95,7 +95,7 @@ VCRT_DEV void primary_finish(const RenderArgs& args, uint32_t pixel, uint32_t sa
 // One warp = kPrimaryRays rays per lane: S consecutive samples (args.primarySamples, a power of two chosen by the host so that few
 // sample slots stay empty: 4 at 500 spp, 1 at the reference's default of 1 spp) of the lane's pixel in kPrimaryRays / S neighbouring
 // 8x4 pixel tiles.
-template <bool FIXED>
+template <bool FIXED, bool BOOK>
 __global__ void __launch_bounds__(kPrimaryThreads, VCRT_PRIMARY_CTAS) primary_scan_kernel(const unsigned char* __restrict__ blobGlobal, RenderArgs args, int scanPad) {
     extern __shared__ __align__(16) unsigned char smem[];
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(kPrimaryThreads, VCRT_PRIMARY_CTAS) primary_sc
             }
             n.rays++; nCand += listCount;
             const int j = rec.index < 0 ? 0 : rec.index;
-            primary_finish<FIXED>(args, pixel, args.sampleOffset + s, at, ray, rec.t, rec.index, sShape[j], sSurf[j], sKind[j], n);
+            primary_finish<FIXED, BOOK>(args, pixel, args.sampleOffset + s, at, ray, rec.t, rec.index, sShape[j], sSurf[j], sKind[j], n);
         }
     }
     // one atomic per warp per counter

@@ -58,7 +58,9 @@ VCRT_DEV void flag_if_ge(uint32_t& m, float q, float s, uint32_t bit) {
 #ifndef VCRT_SCANU_UNROLL
 #define VCRT_SCANU_UNROLL 16   // spheres per unrolled scan body (32 measured: see DESIGN.md 6.1)
 #endif
-template <int THREADS, int PAIRS, int LCAP, bool FIXED, int UNROLL = VCRT_SCANU_UNROLL>
+// BOOK: VCRT_SEMANTICS_BOOK as a compile-time variant - with both scatter routines in one kernel the REFERENCE path carried
+// 32 bytes of spills at its 64-register budget (and the LBVH kernel 24); apart, neither spills.
+template <int THREADS, int PAIRS, int LCAP, bool FIXED, bool BOOK = false, int UNROLL = VCRT_SCANU_UNROLL>
 __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned char* __restrict__ blobGlobal, RenderArgs args, int scanPad) {
     using Cfg = ScanUConfig<THREADS, PAIRS, LCAP>;
     constexpr int R = Cfg::R;
@@ -229,7 +231,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                     philox4x32_10(pixel, args.sampleOffset + ST(SF_SAMPLE, r), pass + 1u, 0u, args.seedLo, args.seedHi, rnd);
                     float u[4] = {u01(rnd[0]), u01(rnd[1]), u01(rnd[2]), u01(rnd[3])};
                     int outcome;   // 0 = unknown material, 1 = scattered, 2 = absorbed by the material (BOOK metal)
-                    if (args.semantics) {
+                    if (BOOK) {
                         BookDraws g; g.pixel = pixel; g.sample = args.sampleOffset + ST(SF_SAMPLE, r); g.event = pass + 1u; g.seedLo = args.seedLo; g.seedHi = args.seedHi;
                         outcome = scatter_book(sShape[rec.index], sSurf[rec.index], sKind[rec.index], rec.t, ray, colour, u, g);
                     } else outcome = scatter(sShape[rec.index], sSurf[rec.index], sKind[rec.index], rec.t, ray, colour, u) ? 1 : 0;
@@ -281,7 +283,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                     state = __float_as_int(ea.w);
                     if (state >= 0) {   // the sample goes on after its first scatter event
                         const float4 eb = __ldcs(args.primary.b + at);
-                        const V3 colour = first_attenuation(sSurf[state], sKind[state], args.semantics);
+                        const V3 colour = first_attenuation(sSurf[state], sKind[state], BOOK ? 1u : 0u);
                         ST(SF_OX, r) = __float_as_uint(ea.x); ST(SF_OY, r) = __float_as_uint(ea.y); ST(SF_OZ, r) = __float_as_uint(ea.z);
                         ST(SF_DX, r) = __float_as_uint(eb.x); ST(SF_DY, r) = __float_as_uint(eb.y); ST(SF_DZ, r) = __float_as_uint(eb.z);
                         ST(SF_CR, r) = __float_as_uint(colour.x); ST(SF_CG, r) = __float_as_uint(colour.y); ST(SF_CB, r) = __float_as_uint(colour.z);

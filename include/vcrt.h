@@ -191,6 +191,41 @@ int cudaStreamElapsed(IN uint32_t fromSlot, IN uint32_t toSlot, OUT float* milli
 /* Writes a scratch buffer larger than the L2 on the layer's stream (timing hygiene between timed renders). */
 int cudaFlushL2(void);
 
+/* ---- a render call that allocates nothing ---- */
+/* No counterpart in the reference: added for callers that cannot call
+   cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It is the in-order exhaustive
+   kernel of VCRT_TRAVERSAL_SIMPLE (every ray tests every sphere exactly, in the caller's order: right for ANY scene), spread
+   over (pixel, run of samples), with all of its scratch memory - the device copy of the scene as a structure of arrays, the
+   partial-sum planes, the counters - in ONE file-scope `static __device__` array of VCRT_NOALLOC_SCRATCH_BYTES that every GPU
+   which loads the library holds until the process exits.  The call makes no cudaMalloc / cudaFree and calls no allocating
+   library routine; it creates no stream or event, does not synchronise and does not touch the state of the other entry points
+   (no cudaUploadScene needed, cudaDownloadImage / cudaGetRenderStats do not see it).
+
+     deviceSpheres  `count` spheres in DEVICE memory of the CURRENT device (the caller's cudaSetDevice, not cudaSelectDevice)
+     camera, params HOST structs, read before the call returns.  Used: width, height, samplesPerPixel, maxDepth, seed,
+                    sampleOffset, totalSamples (0 = samplesPerPixel), semantics, sampleChunks (0 or 1: a pixel's samples summed
+                    strictly in index order; n: n partial sums per pixel, summed in run order).  traversal must be AUTO or SIMPLE,
+                    flags and reserved must be 0.
+     deviceImage    width*height*4 floats in DEVICE memory, the normalised RGBA32F image, the same bits as cudaRender with
+                    the same params (traversal SIMPLE for sampleChunks <= 1, BRUTE / LBVH for n) followed by cudaDownloadImage
+     stream         a cudaStream_t (NULL: the default stream).  The work is ENQUEUED there; the image is complete when the
+                    stream gets past it, and a kernel fault surfaces at the caller's next synchronisation.
+
+   Limits (VCRT_ERROR_INVALID_ARGUMENT with a text that names them): count <= VCRT_NOALLOC_MAX_SPHERES, and
+   width*height * runs <= VCRT_NOALLOC_MAX_PLANE_PIXELS where runs = ceil(spp / ceil(spp / max(sampleChunks, 1))) - 1920x1080
+   in one run, 1280x720 in two, 400x225 in 23.  Host pointers for deviceSpheres / deviceImage are refused.
+   Every call shares the one array, which keeps the last call's contents; the call itself clears what has to start at zero.
+   Two calls that OVERLAP on the GPU (different streams without an ordering between them, two host threads, two processes are
+   fine - they have an array each) race on it: keep the calls of one process on one stream or order them with events.
+   Hits on a texture id outside 1..3 are absorbed as in cudaRender but cannot be reported (nothing is read back).
+   The first call on a device loads the module and looks the array's address up (cudaGetSymbolAddress): make it outside a
+   graph capture. */
+#define VCRT_NOALLOC_MAX_SPHERES 4096u
+#define VCRT_NOALLOC_MAX_PLANE_PIXELS (1u << 21)
+#define VCRT_NOALLOC_SCRATCH_BYTES (256u + VCRT_NOALLOC_MAX_SPHERES * 48u + VCRT_NOALLOC_MAX_PLANE_PIXELS * 16u)   /* 32.2 MiB */
+int cudaRenderNoAlloc(IN const VcrtSphere* deviceSpheres, IN uint32_t count, IN const VcrtCamera* camera,
+                      IN const VcrtRenderParams* params, OUT float* deviceImage, IN size_t imageBytes, IN void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,6 +24,7 @@ VCRT_ERROR_SCENE = -8
 
 VCRT_TRAVERSAL_AUTO, VCRT_TRAVERSAL_BRUTE, VCRT_TRAVERSAL_LBVH, VCRT_TRAVERSAL_SIMPLE = 0, 1, 2, 3
 VCRT_FLAG_ACCUMULATE, VCRT_FLAG_NO_REDUCE, VCRT_FLAG_ALL_REDUCE, VCRT_FLAG_COUNT_STATS = 1, 2, 4, 8
+VCRT_NOALLOC_MAX_SPHERES, VCRT_NOALLOC_MAX_PLANE_PIXELS = 4096, 1 << 21   # cudaRenderNoAlloc: what its static scratch array holds
 
 
 class VcrtSphere(ctypes.Structure):
@@ -93,6 +94,8 @@ PROTOTYPES = {
     "cudaStreamMark": (ctypes.c_int, [ctypes.c_uint32]),
     "cudaStreamElapsed": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(ctypes.c_float)]),
     "cudaFlushL2": (ctypes.c_int, []),
+    "cudaRenderNoAlloc": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint32, ctypes.POINTER(VcrtCamera), ctypes.POINTER(VcrtRenderParams),
+                                         ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]),
     "vcrtDefaultSceneRecipe": (None, [ctypes.POINTER(VcrtSceneRecipe)]),
     "vcrtSceneCapacity": (ctypes.c_uint32, [ctypes.POINTER(VcrtSceneRecipe)]),
     "vcrtGenerateScene": (ctypes.c_int32, [ctypes.POINTER(VcrtSceneRecipe), ctypes.POINTER(VcrtSphere), ctypes.c_uint32]),

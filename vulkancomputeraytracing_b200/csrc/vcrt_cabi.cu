@@ -1092,3 +1092,174 @@ extern "C" int cudaDestroyRenderer(void) {
     cudaComputeImageValid = false; cudaComputeSceneReady = false; cudaComputeDeviceReady = false;
     return VCRT_SUCCESS;
 }
+
+// ------------------------------------------------------------------ cudaRenderNoAlloc: a render call that allocates nothing
+// (include/vcrt.h: no counterpart in the reference; for callers that cannot call cudaMalloc.)  Nothing above this line is
+// used by it except device code (hit_exact, scatter, the Philox generator), makeFrame and fail(); nothing above calls into it.
+//
+// ALL scratch memory of the call lives in this one array.  Every GPU that loads the library holds it until the process exits.
+//     [0, 256)                              counters (Counter enum of vcrt_device.cuh, 64-bit each)
+//     [256, +16 * kNoAllocMaxSpheres)       shape[]  (cx, cy, cz, r)              the scene as a structure of arrays, written
+//     [.., +16 * kNoAllocMaxSpheres)        surf[]   (colour r, g, b, texture.y)  by static_scene_kernel from the caller's AoS
+//     [.., +16 * kNoAllocMaxSpheres)        kind[]   int(texture.x), 4 bytes used per 16
+//     [.., +16 * kNoAllocMaxPlanePixels)    planes[run][pixel]  partial sums of a pixel's runs of samples
+static const uint32_t kNoAllocMaxSpheres = VCRT_NOALLOC_MAX_SPHERES, kNoAllocMaxPlanePixels = VCRT_NOALLOC_MAX_PLANE_PIXELS;
+static const size_t kNoAllocOffShape = 256, kNoAllocOffSurf = kNoAllocOffShape + 16u * (size_t)kNoAllocMaxSpheres,
+                    kNoAllocOffKind = kNoAllocOffSurf + 16u * (size_t)kNoAllocMaxSpheres, kNoAllocOffPlanes = kNoAllocOffKind + 16u * (size_t)kNoAllocMaxSpheres,
+                    kNoAllocBytes = kNoAllocOffPlanes + 16u * (size_t)kNoAllocMaxPlanePixels;
+static_assert(kNoAllocBytes == VCRT_NOALLOC_SCRATCH_BYTES, "the size include/vcrt.h states");
+static_assert(sizeof(unsigned long long) * CTR_COUNT <= 256 && kNoAllocOffPlanes % 256 == 0, "scratch layout");
+static __device__ __align__(256) unsigned char cudaComputeStaticScratch[kNoAllocBytes];
+// In HOST code the name above is only a stand-in for the symbol, not a device address: the address a kernel can use comes from
+// cudaGetSymbolAddress, asked once per device with that device current (each device has its own copy of the array).
+static const int kNoAllocMaxDevices = 64;
+static unsigned char* cudaComputeStaticScratchAddress[kNoAllocMaxDevices];
+
+// caller's AoS (VcrtSphere, 10 floats) -> the SoA the exact test reads; also clears the counters (atomically added to below)
+__global__ void static_scene_kernel(const float* spheres, uint32_t count, unsigned char* scratch) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < (uint32_t)CTR_COUNT) reinterpret_cast<unsigned long long*>(scratch)[j] = 0ull;
+    if (j >= count) return;
+    const float* s = spheres + 10u * (size_t)j;
+    reinterpret_cast<float4*>(scratch + kNoAllocOffShape)[j] = make_float4(s[0], s[1], s[2], s[3]);
+    reinterpret_cast<float4*>(scratch + kNoAllocOffSurf)[j] = make_float4(s[4], s[5], s[6], s[8]);
+    reinterpret_cast<int*>(scratch + kNoAllocOffKind)[j] = (int)s[7];   // switch(int(record.texture.x)), textures.glsl:66
+}
+
+// render_simple_kernel (vcrt_kernel_simple.cuh) with one thread per (pixel, run of samples): blockIdx.z = the run, whose
+// samples [run * sppPerRun, ...) are summed in index order into planes[run][pixel] - the split cudaRender's float modes make.
+__global__ void __launch_bounds__(128) render_static_kernel(DeviceScene scene, RenderArgs args) {
+    const uint32_t px = blockIdx.x * 16 + (threadIdx.x & 15), py = blockIdx.y * 8 + (threadIdx.x >> 4), run = blockIdx.z;
+    unsigned long long rays = 0, exhausted = 0, bad = 0;
+    if (px < args.width && py < args.height) {
+        const uint32_t pixel = py * args.width + px;
+        const uint32_t first = run * args.plan.sppPerRun, last = min(args.spp, first + args.plan.sppPerRun);
+        V3 sum = v3(0.f, 0.f, 0.f);
+        for (uint32_t s = first; s < last; s++) {
+            const uint32_t sample = args.sampleOffset + s;
+            uint32_t rnd[4];
+            philox4x32_10(pixel, sample, 0u, 0u, args.seedLo, args.seedHi, rnd);
+            Ray ray = primary_ray(args.frame, px, py, u01(rnd[0]), u01(rnd[1]));
+            V3 colour = v3(1.f, 1.f, 1.f), result = v3(0.f, 0.f, 0.f);   // bug B7: a path that runs out of depth is black
+            uint32_t pass = 0;
+            for (; pass < args.maxDepth; pass++) {
+                rays++;
+                HitRec rec; rec.t = kTMax; rec.index = -1;
+                const float a = vdot(ray.d, ray.d);
+                for (int i = 0; i < scene.count; i++) hit_exact(__ldg(&scene.shape[i]), i, ray, a, rec, false);
+                if (rec.index < 0) { result = vmul(colour, sky(ray.d)); break; }
+                philox4x32_10(pixel, sample, pass + 1u, 0u, args.seedLo, args.seedHi, rnd);
+                float u[4] = {u01(rnd[0]), u01(rnd[1]), u01(rnd[2]), u01(rnd[3])};
+                const float4 shape = __ldg(&scene.shape[rec.index]), surf = __ldg(&scene.surf[rec.index]);
+                const int kind = __ldg(&scene.kind[rec.index]);
+                int outcome;   // 0 = unknown material, 1 = scattered, 2 = absorbed by the material (BOOK metal)
+                if (args.semantics) {
+                    BookDraws g; g.pixel = pixel; g.sample = sample; g.event = pass + 1u; g.seedLo = args.seedLo; g.seedHi = args.seedHi;
+                    outcome = scatter_book(shape, surf, kind, rec.t, ray, colour, u, g);
+                } else outcome = scatter(shape, surf, kind, rec.t, ray, colour, u) ? 1 : 0;
+                if (outcome != 1) { if (outcome == 0) bad++; break; }
+            }
+            if (pass == args.maxDepth) exhausted++;
+            sum = vadd(sum, result);
+        }
+        args.sums[(size_t)run * args.width * args.height + pixel] = make_float4(sum.x, sum.y, sum.z, 0.f);
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        rays += __shfl_down_sync(0xffffffffu, rays, off);
+        exhausted += __shfl_down_sync(0xffffffffu, exhausted, off);
+        bad += __shfl_down_sync(0xffffffffu, bad, off);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&args.counters[CTR_RAYS], rays);
+        if (exhausted) atomicAdd(&args.counters[CTR_EXHAUSTED], exhausted);
+        if (bad) atomicAdd(&args.counters[CTR_BAD_MATERIAL], bad);
+    }
+}
+
+// combine_planes_kernel + normalise_kernel in one: 0 + plane[0] + plane[1] + ... in run order, / samples, BOOK gamma, alpha 1
+__global__ void static_finish_kernel(float4* image, const float4* planes, uint32_t pixels, uint32_t runs, float samples, int gamma) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pixels) return;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (uint32_t c = 0; c < runs; c++) {
+        const float4 s = planes[(size_t)c * pixels + p];
+        a.x = __fadd_rn(a.x, s.x); a.y = __fadd_rn(a.y, s.y); a.z = __fadd_rn(a.z, s.z);
+    }
+    image[p] = make_float4(to_gamma(__fdiv_rn(a.x, samples), gamma), to_gamma(__fdiv_rn(a.y, samples), gamma), to_gamma(__fdiv_rn(a.z, samples), gamma), 1.0f);
+}
+
+static bool isDevicePointer(const void* p) {
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged;
+}
+
+extern "C" int cudaRenderNoAlloc(IN const VcrtSphere* deviceSpheres, IN uint32_t count, IN const VcrtCamera* camera,
+                                 IN const VcrtRenderParams* p, OUT float* deviceImage, IN size_t imageBytes, IN void* stream) {
+    if (!camera || !p || !deviceImage || (!deviceSpheres && count)) return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRenderNoAlloc: null argument%s", "");
+    if (!p->width || !p->height || !p->samplesPerPixel || p->width > 65535u || p->height > 65535u || p->samplesPerPixel >= (1u << 24))
+        return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRenderNoAlloc: width/height must be 1..65535 and samplesPerPixel 1..2^24-1%s", "");
+    if (p->flags || p->reserved[0] || p->reserved[1]) return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRenderNoAlloc: flags and reserved fields must be 0%s", "");
+    if (p->traversal != VCRT_TRAVERSAL_AUTO && p->traversal != VCRT_TRAVERSAL_SIMPLE)
+        return fail(VCRT_ERROR_UNSUPPORTED, "cudaRenderNoAlloc has the in-order exhaustive kernel only: traversal must be AUTO or SIMPLE%s", "");
+    if (p->semantics > VCRT_SEMANTICS_BOOK) return fail(VCRT_ERROR_INVALID_ARGUMENT, "unknown semantics%s", "");
+    char limits[160];
+    if (count > kNoAllocMaxSpheres) {
+        snprintf(limits, sizeof limits, "%u spheres, the static scratch array holds VCRT_NOALLOC_MAX_SPHERES = %u", count, kNoAllocMaxSpheres);
+        return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRenderNoAlloc: %s", limits);
+    }
+    // the split of cudaRender's float modes: runs of ceil(spp / chunks) samples, and only as many runs as that leaves
+    uint32_t chunks = p->sampleChunks ? p->sampleChunks : 1u;
+    if (chunks > p->samplesPerPixel) chunks = p->samplesPerPixel;
+    const uint32_t perRun = (p->samplesPerPixel + chunks - 1u) / chunks, runs = (p->samplesPerPixel + perRun - 1u) / perRun;
+    const uint64_t pixels = (uint64_t)p->width * p->height;
+    if (pixels * runs > kNoAllocMaxPlanePixels || runs > 65535u) {
+        snprintf(limits, sizeof limits, "%u x %u pixels x %u runs of samples, the static scratch array holds VCRT_NOALLOC_MAX_PLANE_PIXELS = %u (and 65535 runs)",
+                 p->width, p->height, runs, kNoAllocMaxPlanePixels);
+        return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRenderNoAlloc: %s", limits);
+    }
+    if (imageBytes < pixels * sizeof(float4)) return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRenderNoAlloc: image smaller than width*height*16 bytes%s", "");
+
+    // set-up, once per device, with that device current: the device address of the scratch array
+    int device = -1;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return fail(VCRT_ERROR_NO_DEVICE, "no CUDA device available (%s); this library has no CPU path", cudaGetErrorString(e));
+    if (device < 0 || device >= kNoAllocMaxDevices) return fail(VCRT_ERROR_UNSUPPORTED, "cudaRenderNoAlloc: device index beyond 63%s", "");
+    if (!cudaComputeStaticScratchAddress[device]) {
+        int major = 0;
+        CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+        if (major < 10) return fail(VCRT_ERROR_UNSUPPORTED, "device is not sm_100 class%s", "");
+        unsigned char* address = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress((void**)&address, cudaComputeStaticScratch));
+        if (!address) return fail(VCRT_ERROR_CUDA, "cudaGetSymbolAddress gave no address for the scratch array%s", "");
+        cudaComputeStaticScratchAddress[device] = address;
+    }
+    unsigned char* scratch = cudaComputeStaticScratchAddress[device];
+    // a host pointer here would fault in the kernel (or, where the GPU reaches host memory, be silently wrong): refuse it
+    if ((count && !isDevicePointer(deviceSpheres)) || !isDevicePointer(deviceImage))
+        return fail(VCRT_ERROR_INVALID_ARGUMENT, "cudaRenderNoAlloc: deviceSpheres and deviceImage must be device memory%s", "");
+
+    RenderArgs args; memset(&args, 0, sizeof args);
+    const bool book = p->semantics == VCRT_SEMANTICS_BOOK;
+    args.frame = makeFrame(*camera, p->width, p->height, book);
+    args.semantics = p->semantics;
+    args.width = p->width; args.height = p->height; args.spp = p->samplesPerPixel; args.sampleOffset = p->sampleOffset;
+    args.maxDepth = p->maxDepth; args.seedLo = (uint32_t)p->seed; args.seedHi = (uint32_t)(p->seed >> 32);
+    args.chunks = runs; args.plan.sppPerRun = perRun; args.plan.runsPerPixel = runs;
+    args.sums = reinterpret_cast<float4*>(scratch + kNoAllocOffPlanes);
+    args.counters = reinterpret_cast<unsigned long long*>(scratch);
+    DeviceScene scene; memset(&scene, 0, sizeof scene);
+    scene.shape = reinterpret_cast<const float4*>(scratch + kNoAllocOffShape);
+    scene.surf = reinterpret_cast<const float4*>(scratch + kNoAllocOffSurf);
+    scene.kind = reinterpret_cast<const int*>(scratch + kNoAllocOffKind);
+    scene.count = (int)count;
+
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t prepare = count > (uint32_t)CTR_COUNT ? count : (uint32_t)CTR_COUNT;
+    static_scene_kernel<<<(prepare + 127u) / 128u, 128, 0, s>>>(reinterpret_cast<const float*>(deviceSpheres), count, scratch);
+    render_static_kernel<<<dim3((p->width + 15u) / 16u, (p->height + 7u) / 8u, runs), 128, 0, s>>>(scene, args);
+    static_finish_kernel<<<(unsigned int)((pixels + 255u) / 256u), 256, 0, s>>>(reinterpret_cast<float4*>(deviceImage), args.sums, (uint32_t)pixels, runs,
+                                                                               (float)(p->totalSamples ? p->totalSamples : p->samplesPerPixel), book ? 1 : 0);
+    CUDA_TRY(cudaGetLastError());
+    return VCRT_SUCCESS;
+}

@@ -48,7 +48,7 @@ WORKLOADS = {
 }
 FLOP_PER_TEST = 17      # one ray-sphere test of the reference = 17 flop (11 FP32-pipe instructions)
 FLOP_PER_FILTER = 14    # what the path kernel executes per (ray, sphere): 7 FMAs of the conservative filter
-FLOP_PER_PRIMARY_FILTER = 8   # what the primary-visibility kernel executes per (camera ray, sphere): 3 FMAs / multiplies + 1 multiply
+FLOP_PER_PRIMARY_FILTER = 6   # what the primary-visibility kernel executes per (camera ray, sphere): 1 multiply + 2 FMAs, each counted as an FMA-pipe slot of 2 flop
 FLOP_PER_BOX = 24       # LBVH: one box = 6 FMAs + 6 min/max, counted as 2 x 6 + 6 x 2
 TRAVERSALS = {"auto": 0, "brute": 1, "lbvh": 2, "simple": 3}
 KERNEL_NAMES = {1: "render_scanu_kernel", 2: "render_lbvh_flat_kernel", 3: "render_simple_kernel"}

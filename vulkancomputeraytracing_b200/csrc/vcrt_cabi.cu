@@ -244,7 +244,7 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
         }
         cudaError_t ce = cudaMemcpyToSymbolAsync(cSceneHot, chot, (size_t)scanPad * sizeof(float4), 0, cudaMemcpyHostToDevice, cudaComputeStream);
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(cudaComputeStream);
-        // the primary-visibility scan (vcrt_kernel_primary.cuh): centres relative to the camera, (c', |c'|^2 - R2) with
+        // the primary-visibility scan (vcrt_kernel_primary.cuh): centres relative to the camera, (c', sqrt(|c'|^2 - R2)) with
         // R2 = r^2 + kappa(|c'|^2 + r^2); c' is the binary64 difference rounded once, and |c'|^2 is taken from the ROUNDED c'
         for (uint32_t j = 0; j < scanPad && ce == cudaSuccess; j++) {
             if (j >= scanCount) { chot[j] = make_float4(0.f, 0.f, 0.f, INFINITY); continue; }
@@ -255,7 +255,17 @@ extern "C" int cudaUploadScene(IN const VcrtSphere* spheres, IN uint32_t count, 
             const double bound = cc - (r2 + (double)kKappaU * (cc + r2)) * (1.0 + 1.0 / 4194304.0);
             float f = (float)bound;
             if ((double)f > bound) f = nextafterf(f, -INFINITY);   // rounded DOWN: can only let more spheres pass
-            chot[j] = make_float4(rx, ry, rz, f);
+            // The kernel compares |t| with the square root instead of t^2 with f (one packed multiply less per ray pair and
+            // sphere).  fl(t^2) >= f > 0 implies |t| >= sqrt(f) (1 - eps), so with the root scaled by 1 - 2^-22 and rounded down
+            // every ray that passed the squared form still passes; f <= 0 (the camera inside the inflated sphere) and tiny f
+            // (t^2 near the subnormals) always pass.
+            float root = 0.f;
+            if (f > 1e-30f) {
+                const double lower = sqrt((double)f) * (1.0 - 1.0 / 4194304.0);
+                root = (float)lower;
+                if ((double)root > lower) root = nextafterf(root, -INFINITY);
+            }
+            chot[j] = make_float4(rx, ry, rz, root);
         }
         if (ce == cudaSuccess) ce = cudaMemcpyToSymbolAsync(cPrimaryHot, chot, (size_t)scanPad * sizeof(float4), 0, cudaMemcpyHostToDevice, cudaComputeStream);
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(cudaComputeStream);

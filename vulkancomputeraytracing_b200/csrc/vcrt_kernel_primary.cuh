@@ -9,10 +9,11 @@
       * they share their origin, the camera (shader.comp:50 `ray(center, ...)`).  With the sphere centres stored relative to the
         camera, c' = c - o, the conservative filter of the brute-force scan (vcrt_kernel_scanu.cuh)
             |c - o|^2 - ((c - o).dh)^2 <= R2
-        needs no per-ray origin terms: t = c'.dh (3 packed FP32 operations), t^2 >= |c'|^2 - R2 (1 packed multiply; the right-hand
-        side is one scalar per sphere).  4 packed operations per ray pair and sphere instead of 7, and with no path state to
-        keep, a thread scans for FOUR rays at once, so the per-sphere overhead (two LDCU.64, max, compare, flag) is shared by 4
-        tests instead of 2;
+        needs no per-ray origin terms: t = c'.dh (3 packed FP32 operations), |t| >= sqrt(|c'|^2 - R2) (no arithmetic at all: the
+        right-hand side is one scalar per sphere, the absolute value an operand modifier of the max over the thread's rays).
+        3 packed operations per ray pair and sphere instead of 7 (4 while the test was t^2 >= |c'|^2 - R2), and with no path
+        state to keep, a thread scans for FOUR rays at once, so the per-sphere overhead (two LDCU.64, max, compare, flag) is
+        shared by 4 tests instead of 2;
       * they are coherent: the 32 lanes of a warp work on one 8x4 pixel tile, so in the shading that follows they mostly meet
         the same sphere and material: 31.8 of 32 lanes active (ncu) where the shading phase of the path kernel runs at 12 - 15.
 
@@ -33,7 +34,9 @@
     from the ray's line satisfies D^2 <= r^2 + 18 eps (|oc|^2 + r^2) (vcrt_kernel_scanu.cuh).  Here c' is rounded from the
     binary64 difference (relative error eps/2 per component), |dh| = 1 +- 4 eps, the dot product and the square add <= 10 eps
     t^2, so fl(t^2) >= |oc|^2 - r^2 - 34 eps (|oc|^2 + r^2) for every acceptable sphere, and the table holds
-    |c'|^2 - r^2 - kappa (|c'|^2 + r^2) rounded down with kappa = 2^-16 = 256 eps.  Extra survivors cost time, never correctness.
+    |c'|^2 - r^2 - kappa (|c'|^2 + r^2) rounded down with kappa = 2^-16 = 256 eps - as its square root, scaled by 1 - 2^-22 and
+    rounded down again, which passes every ray the squared comparison passes (cudaUploadScene).  Extra survivors cost time,
+    never correctness.
 
     Rays outside the tame range (vcrt_device.cuh) and threads whose candidate list overflows are written as kPrimaryUntraced:
     the path kernel starts those samples at the camera itself, the old way.
@@ -43,7 +46,7 @@
 
 namespace vcrt {
 
-__constant__ float4 cPrimaryHot[kMaxConstSpheres];     // (c'x, c'y, c'z, |c'|^2 - R2 rounded down), c' = centre - camera; padding (0,0,0,+inf)
+__constant__ float4 cPrimaryHot[kMaxConstSpheres];     // (c'x, c'y, c'z, sqrt(|c'|^2 - R2) rounded down; 0 = always passes), c' = centre - camera; padding (0,0,0,+inf)
 
 constexpr int kPrimaryThreads = 256;
 #ifndef VCRT_PRIMARY_CTAS
@@ -160,7 +163,7 @@ __global__ void __launch_bounds__(kPrimaryThreads, VCRT_PRIMARY_CTAS) primary_sc
         u64 dxp[kPrimaryPairs], dyp[kPrimaryPairs], dzp[kPrimaryPairs];
 #pragma unroll
         for (int p = 0; p < kPrimaryPairs; p++) { dxp[p] = pack2(dh[2 * p][0], dh[2 * p + 1][0]); dyp[p] = pack2(dh[2 * p][1], dh[2 * p + 1][1]); dzp[p] = pack2(dh[2 * p][2], dh[2 * p + 1][2]); }
-        // the scan: per sphere two LDCU.64, 4 packed FP32 operations per ray pair, a max over the thread's rays and one compare
+        // the scan: per sphere two LDCU.64, 3 packed FP32 operations per ray pair, a max of |t| over the thread's rays and one compare
         uint32_t listCount = 0u;
         auto scan_block = [&]<int U>(int at) -> uint32_t {
             uint32_t mEven = 0u, mOdd = 0u;
@@ -169,15 +172,14 @@ __global__ void __launch_bounds__(kPrimaryThreads, VCRT_PRIMARY_CTAS) primary_sc
                 (void)VCRT_CHECK(args.counters, at + u < scanPad && at + u < kMaxConstSpheres);
                 const float4 s = cPrimaryHot[at + u];
                 const u64 cx = pack2(s.x, s.x), cy = pack2(s.y, s.y), cz = pack2(s.z, s.z);
-                float qmax = -__int_as_float(0x7f800000);
+                float tmax = 0.f;   // max |t| over the thread's rays (the absolute values are operand modifiers of FMNMX)
 #pragma unroll
                 for (int p = 0; p < kPrimaryPairs; p++) {
                     u64 t = fmul2(cz, dzp[p]); t = ffma2(cy, dyp[p], t); t = ffma2(cx, dxp[p], t);
-                    const u64 q = fmul2(t, t);
-                    float q0, q1; unpack2(q, q0, q1);
-                    qmax = fmaxf(qmax, fmaxf(q0, q1));
+                    float t0, t1; unpack2(t, t0, t1);
+                    tmax = p == 0 ? fmaxf(fabsf(t0), fabsf(t1)) : fmaxf(tmax, fmaxf(fabsf(t0), fabsf(t1)));
                 }
-                flag_if_ge(u & 1 ? mOdd : mEven, qmax, s.w, 1u << u);
+                flag_if_ge(u & 1 ? mOdd : mEven, tmax, s.w, 1u << u);
             }
             return mEven | mOdd;
         };

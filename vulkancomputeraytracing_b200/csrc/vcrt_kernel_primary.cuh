@@ -55,6 +55,10 @@ constexpr int kPrimaryThreads = 256;
 #ifndef VCRT_PRIMARY_RAYS
 #define VCRT_PRIMARY_RAYS 4
 #endif
+#ifndef VCRT_PRIMARY_SHADE_UNROLL
+#define VCRT_PRIMARY_SHADE_UNROLL 1
+#endif
+constexpr int kPrimaryShadeUnroll = VCRT_PRIMARY_SHADE_UNROLL;   // rays of a thread whose exact tests and first scatter events are interleaved: 2 / 4 measured 16 / 29 % slower (primary kernel 21.1 -> 24.5 / 27.2 ms at 1080p x 128 spp)
 constexpr int kPrimaryRays = VCRT_PRIMARY_RAYS;        // samples of one pixel per thread (even)
 constexpr int kPrimaryPairs = kPrimaryRays / 2;
 constexpr int kPrimaryListCap = 40;
@@ -203,7 +207,7 @@ __global__ void __launch_bounds__(kPrimaryThreads, VCRT_PRIMARY_CTAS) primary_sc
         // exact tests (the reference's arithmetic, functions.glsl:14-33) of the survivors in ascending index, then the "always"
         // spheres; then the first scatter event
         const bool overflow = listCount > (uint32_t)kPrimaryListCap;
-#pragma unroll 1
+#pragma unroll kPrimaryShadeUnroll
         for (int k = 0; k < kPrimaryRays; k++) {
             uint32_t tile, s, px, py;
             if (!ray_slot(k, tile, s, px, py)) continue;

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanw_kernel(const unsigned
             if (id >= totalItems) { WS(WF_PIXEL, r, t) = kIdle; return false; }
             uint32_t chunk, pid, px, py;
             item_to_run(args.plan, id, chunk, pid);
-            if (!item_to_pixel(args.plan.tilesX, args.width, args.height, pid, px, py)) continue;
+            if (!item_to_pixel(args.plan, args.width, args.height, pid, px, py)) continue;
             uint32_t s0 = chunk * sppPerChunk, s1 = min(args.spp, s0 + sppPerChunk);
             if (s0 >= s1) continue;
             WS(WF_PIXEL, r, t) = py * args.width + px;

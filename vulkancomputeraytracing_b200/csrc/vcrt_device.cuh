@@ -123,6 +123,7 @@ struct ItemPlan {
     uint32_t tileStride;      // consecutive tiles of the numbering are this many tiles apart in the image (coprime with the tile count)
     uint32_t tiles;           // pixelsPadded / 32
     float invTiles;
+    float invTilesX;          // for tile -> (row, column) of tiles without an integer division (25 instructions)
 };
 
 // What the primary-visibility kernels (vcrt_kernel_primary.cuh) hand to the path kernels: every sample of a launch after its
@@ -197,6 +198,11 @@ __device__ __forceinline__ void item_to_run(const ItemPlan& plan, uint32_t id, u
         udiv_small((pid >> 5) * plan.tileStride, plan.tiles, plan.invTiles, tile);
         pid = (tile << 5) | (pid & 31u);
     }
+}
+
+// tile index -> (column, row) of 8x4 tiles
+__device__ __forceinline__ void tile_to_xy(const ItemPlan& plan, uint32_t tile, uint32_t& tx, uint32_t& ty) {
+    ty = udiv_small(tile, plan.tilesX, plan.invTilesX, tx);
 }
 
 constexpr uint32_t kFlagCountStats = 1u << 3;   // VCRT_FLAG_COUNT_STATS of include/vcrt.h

@@ -112,7 +112,10 @@ VCRT_DEV void hit_ordered(float4 shape, int device, uint32_t orig, const Ray& r,
 constexpr float kLbvhK = LBVH_K_EPS * 5.9604644775390625e-08f;   // K = 32 eps (L^2 + rmax^2), eps = 2^-24 (file header)
 
 VCRT_DEV float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-VCRT_DEV float sqrt_approx(float x) { float r; asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+// an upper-bound-friendly approximate root in ONE instruction: the .ftz form needs no subnormal scaling around MUFU.SQRT (3 extra
+// instructions each, 5 roots per ray), and clamping the argument to the smallest normal keeps the result >= the true root where
+// .ftz would have flushed it to 0 (the roots only ever ADD to the widening: too large is conservative)
+VCRT_DEV float sqrt_approx(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaxf(x, 1.17549435e-38f))); return r; }
 
 struct LbvhCounts { uint32_t rays, nodes, tests, exhausted, bad; unsigned long long* counters; };
 
@@ -225,7 +228,7 @@ template <bool FIXED, bool STATS, bool BOOK = false>   // BOOK: VCRT_SEMANTICS_B
 __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhScene scene, RenderArgs args) {
     const uint32_t pixels = args.width * args.height;
     const uint32_t sppPerChunk = args.plan.sppPerRun;   // host-made plan (vcrt_device.cuh)
-    const uint32_t tilesX = args.plan.tilesX, totalItems = args.plan.totalItems;
+    const uint32_t totalItems = args.plan.totalItems;
     LbvhCounts n = {0u, 0u, 0u, 0u, 0u, args.counters};
     int stack[65];
 
@@ -254,7 +257,9 @@ __global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhS
                 if (item >= totalItems) break;
                 uint32_t pid;
                 item_to_run(args.plan, item, chunk, pid);
-                const uint32_t tile = pid >> 5, within = pid & 31u, ty = tile / tilesX, tx = tile - ty * tilesX;
+                const uint32_t tile = pid >> 5, within = pid & 31u;
+                uint32_t tx, ty;
+                tile_to_xy(args.plan, tile, tx, ty);
                 px = tx * 8u + (within & 7u); py = ty * 4u + (within >> 3);
                 if (px >= args.width || py >= args.height) continue;
                 s = chunk * sppPerChunk; s1 = min(args.spp, s + sppPerChunk);

@@ -140,7 +140,8 @@ __global__ void __launch_bounds__(kPrimaryThreads, VCRT_PRIMARY_CTAS) primary_sc
         // ray k of the thread: sample (k mod S) of the group, tile (k / S) of the group
         auto ray_slot = [&](int k, uint32_t& tile, uint32_t& s, uint32_t& px, uint32_t& py) -> bool {
             tile = tileGroup * tPer + ((uint32_t)k >> sShift); s = (sampleGroup << sShift) + ((uint32_t)k & (sPer - 1u));
-            const uint32_t ty = tile / args.plan.tilesX, tx = tile - ty * args.plan.tilesX;
+            uint32_t tx, ty;
+            tile_to_xy(args.plan, tile, tx, ty);
             px = tx * 8u + (lane & 7u); py = ty * 4u + (lane >> 3);
             return unit < units && tile < tiles && s < args.spp && px < args.width && py < args.height;
         };

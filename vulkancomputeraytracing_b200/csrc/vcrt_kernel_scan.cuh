@@ -104,9 +104,9 @@ struct ScanConfig {
 constexpr uint32_t kIdle = 0xffffffffu;
 
 // Item id -> pixel.  Items walk the image in 8x4 tiles so the 32 lanes of a warp start on one tile.
-VCRT_DEV bool item_to_pixel(uint32_t tilesX, uint32_t width, uint32_t height, uint32_t id, uint32_t& px, uint32_t& py) {
-    uint32_t tile = id >> 5, within = id & 31u;
-    uint32_t ty = tile / tilesX, tx = tile - ty * tilesX;
+VCRT_DEV bool item_to_pixel(const ItemPlan& plan, uint32_t width, uint32_t height, uint32_t id, uint32_t& px, uint32_t& py) {
+    uint32_t tile = id >> 5, within = id & 31u, tx, ty;
+    tile_to_xy(plan, tile, tx, ty);
     px = tx * 8u + (within & 7u);
     py = ty * 4u + (within >> 3);
     return px < width && py < height;
@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scan_kernel(const unsigned 
             if (id >= totalItems) { ST(SF_PIXEL, r) = kIdle; return false; }
             uint32_t chunk, pid, px, py;
             item_to_run(args.plan, id, chunk, pid);
-            if (!item_to_pixel(args.plan.tilesX, args.width, args.height, pid, px, py)) continue;
+            if (!item_to_pixel(args.plan, args.width, args.height, pid, px, py)) continue;
             uint32_t s0 = chunk * sppPerChunk, s1 = min(args.spp, s0 + sppPerChunk);
             if (s0 >= s1) continue;
             ST(SF_PIXEL, r) = py * args.width + px;

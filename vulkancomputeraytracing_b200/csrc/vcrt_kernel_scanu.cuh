@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
             if (id >= totalItems) { ST(SF_PIXEL, r) = kIdle; return false; }
             uint32_t chunk, pid, px, py;
             item_to_run(args.plan, id, chunk, pid);
-            if (!item_to_pixel(args.plan.tilesX, args.width, args.height, pid, px, py)) continue;
+            if (!item_to_pixel(args.plan, args.width, args.height, pid, px, py)) continue;
             uint32_t s0 = chunk * sppPerChunk, s1 = min(args.spp, s0 + sppPerChunk);
             if (s0 >= s1) continue;
             ST(SF_PIXEL, r) = py * args.width + px;

@@ -12,7 +12,7 @@ namespace vcrt {
 
 // STATS: the VCRT_FLAG_COUNT_STATS counters are a compile-time variant here (a run-time test costs this kernel 2 %)
 template <bool FIXED, bool STATS>
-__global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_kernel(BvhScene scene, RenderArgs args) {
+__global__ void __launch_bounds__(256, 4) render_lbvh_kernel(BvhScene scene, RenderArgs args) {
     const uint32_t pixels = args.width * args.height;
     const uint32_t sppPerChunk = args.plan.sppPerRun;   // host-made plan (vcrt_device.cuh)
     // items walk the image in 8x4 pixel tiles so a warp starts on one tile

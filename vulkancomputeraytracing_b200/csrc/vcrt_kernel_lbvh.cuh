@@ -68,9 +68,14 @@ struct BvhScene {
     float halfInvRadiusMin;       // >= 1 / (2 radiusMin), rounded up
 };
 
+// Resident CTAs of 256 per SM that the REGISTER BUDGET of the default variant (fixed-point sums, REFERENCE semantics) is set for.
+// With 3 (<= 85 registers) ptxas still allocates 64, so four CTAs stay resident, but it schedules the kernel differently: +2.6 % at
+// 485 / 10 k / 100 k spheres and on the stress scene against a budget of 4 (2: +1.6 %, 5: 92 bytes of spills, -0.6 %).  The
+// strict-order and BOOK variants take 69 / 80 registers under that budget and lose 1 %, so they keep 4.
 #ifndef LBVH_BLOCKS
-#define LBVH_BLOCKS 4   // resident CTAs of 256 per SM the register budget is set for (64 registers; measured 1.4 % faster than 3)
+#define LBVH_BLOCKS 3
 #endif
+constexpr int lbvh_min_blocks(bool fixed, bool book) { return fixed && !book ? LBVH_BLOCKS : 4; }
 
 struct OrderedHit { float t; int device; uint32_t orig; };
 
@@ -225,7 +230,7 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
 }
 
 template <bool FIXED, bool STATS, bool BOOK = false>   // BOOK: VCRT_SEMANTICS_BOOK as a compile-time variant (see render_scanu_kernel)
-__global__ void __launch_bounds__(256, LBVH_BLOCKS) render_lbvh_flat_kernel(BvhScene scene, RenderArgs args) {
+__global__ void __launch_bounds__(256, lbvh_min_blocks(FIXED, BOOK)) render_lbvh_flat_kernel(BvhScene scene, RenderArgs args) {
     const uint32_t pixels = args.width * args.height;
     const uint32_t sppPerChunk = args.plan.sppPerRun;   // host-made plan (vcrt_device.cuh)
     const uint32_t totalItems = args.plan.totalItems;

@@ -826,6 +826,7 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         plan.invLastBand = plan.lastBandPixels ? nextafterf(1.0f / (float)plan.lastBandPixels, 0.f) : 0.f;
         plan.tiles = plan.pixelsPadded / 32u; plan.invTiles = nextafterf(1.0f / (float)plan.tiles, 0.f);
         plan.invTilesX = nextafterf(1.0f / (float)plan.tilesX, 0.f);
+        plan.invWidth = nextafterf(1.0f / (float)p->width, 0.f);
         plan.tileStride = 1u;
         if (traversal == VCRT_TRAVERSAL_BRUTE && fullBands >= 1u) {
             uint32_t stride = plan.tiles / (kBandPixels / 32u);

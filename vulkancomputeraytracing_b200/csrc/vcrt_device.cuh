@@ -124,6 +124,7 @@ struct ItemPlan {
     uint32_t tiles;           // pixelsPadded / 32
     float invTiles;
     float invTilesX;          // for tile -> (row, column) of tiles without an integer division (25 instructions)
+    float invWidth;           // for pixel index -> (x, y)
 };
 
 // What the primary-visibility kernels (vcrt_kernel_primary.cuh) hand to the path kernels: every sample of a launch after its
@@ -203,6 +204,11 @@ __device__ __forceinline__ void item_to_run(const ItemPlan& plan, uint32_t id, u
 // tile index -> (column, row) of 8x4 tiles
 __device__ __forceinline__ void tile_to_xy(const ItemPlan& plan, uint32_t tile, uint32_t& tx, uint32_t& ty) {
     ty = udiv_small(tile, plan.tilesX, plan.invTilesX, tx);
+}
+
+// pixel index (y * width + x) -> (x, y)
+__device__ __forceinline__ void pixel_to_xy(const ItemPlan& plan, uint32_t width, uint32_t pixel, uint32_t& px, uint32_t& py) {
+    py = udiv_small(pixel, width, plan.invWidth, px);
 }
 
 constexpr uint32_t kFlagCountStats = 1u << 3;   // VCRT_FLAG_COUNT_STATS of include/vcrt.h

@@ -274,7 +274,8 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                 }
                 pixel = ST(SF_PIXEL, r);
                 const uint32_t sLocal = ST(SF_SAMPLE, r);
-                const uint32_t py = pixel / args.width, px = pixel - py * args.width;
+                uint32_t px, py;
+                pixel_to_xy(args.plan, args.width, pixel, px, py);
                 int state = kPrimaryUntraced;
                 if (args.primary.a) {
                     const size_t at = (size_t)sLocal * args.plan.pixelsPadded + padded_pixel_id(args.plan.tilesX, px, py);

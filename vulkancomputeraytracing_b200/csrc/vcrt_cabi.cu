@@ -109,7 +109,7 @@ static int ensureDevice(void) {
     CUDA_TRY(cudaStreamCreateWithFlags(&cudaComputeStream, cudaStreamNonBlocking));
     for (int i = 0; i < 4; i++) CUDA_TRY(cudaEventCreate(&cudaComputeEvents[i]));
     CUDA_TRY(cudaMalloc(&cudaComputeCounters, sizeof(unsigned long long) * CTR_COUNT));
-    CUDA_TRY(cudaMalloc(&cudaComputeWorkCounter, sizeof(unsigned int)));
+    CUDA_TRY(cudaMalloc(&cudaComputeWorkCounter, 4 * sizeof(unsigned int)));   // [0] the item dispenser, [2], [3] the cursors of the compact hand-over list
     cudaComputeDeviceReady = true;
     return VCRT_SUCCESS;
 }
@@ -720,6 +720,8 @@ static int launchScanU(const RenderArgs& args, uint32_t* launches) {
     using Cfg = ScanUConfig<THREADS, PAIRS, LCAP>;
     const size_t smem = Cfg::smem_bytes(cudaComputeSceneHeader.bytes);
     auto kernel = args.semantics ? render_scanu_kernel<THREADS, PAIRS, LCAP, FIXED, true> : render_scanu_kernel<THREADS, PAIRS, LCAP, FIXED, false>;
+    if constexpr (FIXED)   // after a primary-visibility pass the samples come from its compact list
+        if (args.primary.cursors) kernel = args.semantics ? render_scanu_kernel<THREADS, PAIRS, LCAP, true, true, true> : render_scanu_kernel<THREADS, PAIRS, LCAP, true, false, true>;
     CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const unsigned int grid = (unsigned int)cudaComputeSmCount;   // persistent: one CTA per SM
     const unsigned int firstDynamicItem = grid * Cfg::R * THREADS;
@@ -863,6 +865,10 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
         if (passes < byItems) passes = byItems;
         const uint32_t byRuns = (p->samplesPerPixel / perRunFixed) / ((1u << 22) - 2u) + 1u;   // runs per pixel and launch stay below 2^22
         if (passes < byRuns) passes = byRuns;
+        if (usePrimary) {   // the compact hand-over list keeps the sample index of a launch in 21 bits
+            const uint32_t bySamples = p->samplesPerPixel / (kPrimaryMaxLaunchSamples - 1u) + 1u;
+            if (passes < bySamples) passes = bySamples;
+        }
         if (passes < 1u) passes = 1u;
     }
     ItemPlan plan;
@@ -912,6 +918,7 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
     args.primary.a = usePrimary ? cudaComputePrimary : nullptr;
     args.primary.b = usePrimary ? cudaComputePrimary + cudaComputePrimaryCapacity : nullptr;
     args.primary.entries = usePrimary ? cudaComputePrimaryCapacity : 0;
+    args.primary.cursors = usePrimary && fixedMode ? cudaComputeWorkCounter + 2 : nullptr;   // fixed-point sums: the hand-over is a compact list
 
     uint32_t launches = 0, timedPasses = 0;
     CUDA_TRY(cudaEventRecord(cudaComputeEvents[0], cudaComputeStream));
@@ -945,6 +952,7 @@ extern "C" int cudaRender(IN const VcrtRenderParams* p) {
                 while (cudaComputePassEventCount < 2 * (pass + 1)) { CUDA_TRY(cudaEventCreate(&cudaComputePassEvents[cudaComputePassEventCount])); cudaComputePassEventCount++; }
                 CUDA_TRY(cudaEventRecord(cudaComputePassEvents[2 * pass], cudaComputeStream));
             }
+            if (args.primary.cursors) CUDA_TRY(cudaMemsetAsync(args.primary.cursors, 0, 2 * sizeof(unsigned int), cudaComputeStream));
             rc = fixedMode ? launchPrimaryScan<true>(args, &launches) : launchPrimaryScan<false>(args, &launches);
             if (rc) return rc;
             if (timed) { CUDA_TRY(cudaEventRecord(cudaComputePassEvents[2 * pass + 1], cudaComputeStream)); timedPasses = pass + 1; }

@@ -133,10 +133,18 @@ struct ItemPlan {
 //   a = (origin of the scattered ray, state as bits)     state >= 0: device index of the sphere that was hit - the path goes on
 //   b = (direction of the scattered ray, 0)                          with this ray, throughput = that sphere's attenuation, pass 1
 //                                                         state < 0: one of the values below
-struct PrimaryBuffer { float4* a; float4* b; size_t entries; };   // entries: capacity of each plane (checked build)
+//
+// Fixed-point mode (the sums do not care about the order of the samples) uses the buffer as a COMPACT list instead: the primary
+// kernel appends only the samples that go on (cursors[0] counts them; a sample that ended has been added to the sums and leaves
+// no entry), the path kernel takes entries in list order (cursors[1]):
+//   a = (origin, sample index within the launch << 11 | device index of the sphere that was hit)     b = (direction, pixel index)
+// with sphere = kPrimaryCameraStart for a sample that was not pre-traced.  A finished slot of the path kernel then costs one
+// atomic and two 16-byte loads - no work-item decoding, no entry for the 17 % of the samples that end at their first ray.
+struct PrimaryBuffer { float4* a; float4* b; size_t entries; unsigned int* cursors; };   // entries: capacity of each plane
+constexpr uint32_t kPrimarySphereBits = 11u, kPrimaryCameraStart = (1u << kPrimarySphereBits) - 1u;   // 1792 + 64 spheres at most reach these kernels
+constexpr uint32_t kPrimaryMaxLaunchSamples = 1u << (32u - kPrimarySphereBits);                         // samples per pixel and launch the word can hold
 constexpr int kPrimaryEnded = -1;       // the sample ended at its first ray (sky / absorbed / depth 1): b.xyz = its radiance (strict-order sums)
 constexpr int kPrimaryUntraced = -2;    // not pre-traced (a ray outside the tame range, a candidate-list overflow): the path kernel starts at the camera
-constexpr int kPrimaryDone = -3;        // ended AND already added to the fixed-point sums by the primary kernel: nothing left to do
 
 struct RenderArgs {
     Frame frame;

@@ -60,8 +60,11 @@ VCRT_DEV void flag_if_ge(uint32_t& m, float q, float s, uint32_t bit) {
 #endif
 // BOOK: VCRT_SEMANTICS_BOOK as a compile-time variant - with both scatter routines in one kernel the REFERENCE path carried
 // 32 bytes of spills at its 64-register budget (and the LBVH kernel 24); apart, neither spills.
-template <int THREADS, int PAIRS, int LCAP, bool FIXED, bool BOOK = false, int UNROLL = VCRT_SCANU_UNROLL>
+// COMPACT (fixed-point sums + primary-visibility pass): new samples come from the compact list of vcrt_device.cuh instead of the
+// work-item dispenser - one atomic and two 16-byte loads per finished slot.
+template <int THREADS, int PAIRS, int LCAP, bool FIXED, bool BOOK = false, bool COMPACT = false, int UNROLL = VCRT_SCANU_UNROLL>
 __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned char* __restrict__ blobGlobal, RenderArgs args, int scanPad) {
+    static_assert(FIXED || !COMPACT, "the compact list is the hand-over of fixed-point mode");
     using Cfg = ScanUConfig<THREADS, PAIRS, LCAP>;
     constexpr int R = Cfg::R;
     extern __shared__ __align__(16) unsigned char smem[];
@@ -112,6 +115,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
         }
     };
     const int scanCount = (int)hdr.scanCount, count = (int)hdr.count;
+    const uint32_t listed = COMPACT ? __ldcg(&args.primary.cursors[0]) : 0u;   // entries the primary kernel left (it has finished: stream order)
     const float kPosInf = __int_as_float(0x7f800000);
     uint32_t listCount = 0, exhaustMask = 0;   // candidates of this thread this round; slots that need the exhaustive exact scan
 
@@ -250,7 +254,31 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                 haveResult = true;
             }
             // ---- the sample in the slot is finished (or there was none): add it to the sums, take the next one
-            for (;;) {
+            if constexpr (COMPACT) {
+                if (haveResult) add_fixed(args, pixel, result);
+                const uint32_t at = atomicAdd(&args.primary.cursors[1], 1u);
+                if (at >= listed || !VCRT_CHECK(args.counters, at < args.primary.entries)) { ST(SF_PIXEL, r) = kIdle; continue; }   // the list is used up: the slot idles
+                const float4 ea = __ldcs(args.primary.a + at), eb = __ldcs(args.primary.b + at);
+                const uint32_t word = __float_as_uint(ea.w), sphere = word & kPrimaryCameraStart;
+                pixel = __float_as_uint(eb.w);
+                ST(SF_PIXEL, r) = pixel; ST(SF_SAMPLE, r) = word >> kPrimarySphereBits;
+                if (sphere != kPrimaryCameraStart && VCRT_CHECK(args.counters, (int)sphere < count)) {   // the sample goes on after its first scatter event
+                    const V3 colour = first_attenuation(sSurf[sphere], sKind[sphere], BOOK ? 1u : 0u);
+                    ST(SF_OX, r) = __float_as_uint(ea.x); ST(SF_OY, r) = __float_as_uint(ea.y); ST(SF_OZ, r) = __float_as_uint(ea.z);
+                    ST(SF_DX, r) = __float_as_uint(eb.x); ST(SF_DY, r) = __float_as_uint(eb.y); ST(SF_DZ, r) = __float_as_uint(eb.z);
+                    ST(SF_CR, r) = __float_as_uint(colour.x); ST(SF_CG, r) = __float_as_uint(colour.y); ST(SF_CB, r) = __float_as_uint(colour.z);
+                    ST(SF_PASS, r) = 1u;
+                } else {   // not pre-traced (a ray outside the tame range, a candidate-list overflow): start at the camera (shader.comp:46-52)
+                    uint32_t px, py, rnd[4];
+                    pixel_to_xy(args.plan, args.width, pixel, px, py);
+                    philox4x32_10(pixel, args.sampleOffset + (word >> kPrimarySphereBits), 0u, 0u, args.seedLo, args.seedHi, rnd);
+                    const Ray ray = primary_ray(args.frame, px, py, u01(rnd[0]), u01(rnd[1]));
+                    ST(SF_OX, r) = __float_as_uint(ray.o.x); ST(SF_OY, r) = __float_as_uint(ray.o.y); ST(SF_OZ, r) = __float_as_uint(ray.o.z);
+                    ST(SF_DX, r) = __float_as_uint(ray.d.x); ST(SF_DY, r) = __float_as_uint(ray.d.y); ST(SF_DZ, r) = __float_as_uint(ray.d.z);
+                    ST(SF_CR, r) = ST(SF_CG, r) = ST(SF_CB, r) = __float_as_uint(1.0f);
+                    ST(SF_PASS, r) = 0u;
+                }
+            } else for (;;) {
                 if (haveResult) {   // shader.comp:53: color.rgb += ray_color(r), in sample order within the item
                     haveResult = false;
                     uint32_t s = ST(SF_SAMPLE, r);
@@ -277,7 +305,7 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                 uint32_t px, py;
                 pixel_to_xy(args.plan, args.width, pixel, px, py);
                 int state = kPrimaryUntraced;
-                if (args.primary.a) {
+                if (!FIXED && args.primary.a) {   // strict-order modes: one entry per sample (fixed-point mode: the COMPACT branch above)
                     const size_t at = (size_t)sLocal * args.plan.pixelsPadded + padded_pixel_id(args.plan.tilesX, px, py);
                     (void)VCRT_CHECK(args.counters, at < args.primary.entries);
                     const float4 ea = __ldcs(args.primary.a + at);
@@ -291,7 +319,6 @@ __global__ void __launch_bounds__(THREADS, 1) render_scanu_kernel(const unsigned
                         ST(SF_PASS, r) = 1u;
                         break;
                     }
-                    if (state == kPrimaryDone) { result = v3(0.f, 0.f, 0.f); haveResult = true; continue; }   // already in the fixed-point sums
                     if (state == kPrimaryEnded) {
                         const float4 eb = __ldcs(args.primary.b + at);
                         result = v3(eb.x, eb.y, eb.z); haveResult = true; continue;

@@ -128,6 +128,11 @@ def test_bit_exact_on_adversarial_scenes(oracle, vcrt, traversal, case):
         assert_same(gpu, st, cpu, cst)
         if case == "dense_line" and traversal == BRUTE:
             assert st.listOverflows > 0                          # the exhaustive fallback really ran
+        # the default accumulation (fixed-point sums; brute force: primary pass + compact hand-over list, whose "not pre-traced"
+        # entries the overflowing lists of dense_line produce): the same paths, sums that differ by their rounding only
+        fixed, sf = host.render(96, 64, 2, depth=20, traversal=traversal)
+        assert sf.rays == st.rays and sf.depthExhausted == st.depthExhausted
+        assert np.abs(fixed - gpu).max() <= 2.0 ** -22 * max(1.0, float(np.abs(gpu[..., :3]).max()))
     finally:
         host.destroy()
 

@@ -619,6 +619,7 @@ static int ensureBvh(void) {
     const size_t offLeafShape = off; off += alignUp(sizeof(float4) * n);
     const size_t offLeafOrig = off; off += alignUp(sizeof(uint32_t) * n);
     const size_t offLeafDevice = off; off += alignUp(sizeof(uint32_t) * n);
+    const size_t offLeafRecord = off; off += alignUp(sizeof(LeafRecord) * n);
     const size_t offNodes = off; off += alignUp(sizeof(BvhNode) * nodes);
     const size_t offOctNodes = off; off += alignUp(sizeof(BvhNode) * nodes * 8);
     const size_t offParent = off; off += alignUp(sizeof(int) * (2 * (size_t)n));
@@ -647,6 +648,7 @@ static int ensureBvh(void) {
     unsigned long long* keysIn = (unsigned long long*)(arena + offKeysIn);
     g.keys = keysIn;
     g.leafShape = (float4*)(arena + offLeafShape); g.leafOrig = (uint32_t*)(arena + offLeafOrig); g.leafDevice = (uint32_t*)(arena + offLeafDevice);
+    g.leafRecord = (LeafRecord*)(arena + offLeafRecord);
     g.nodes = (BvhNode*)(arena + offNodes); g.octNodes = (BvhNode*)(arena + offOctNodes); g.parent = (int*)(arena + offParent); g.bounds = (float*)(arena + offBounds);
     g.arrivals = (unsigned int*)(arena + offArrivals);
     const unsigned int blocks = (n + 255) / 256;
@@ -661,7 +663,7 @@ static int ensureBvh(void) {
     }
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaStreamSynchronize(cudaComputeStream));
-    bs.nodes = g.nodes; bs.octNodes = g.octNodes; bs.leafShape = g.leafShape; bs.leafOrig = g.leafOrig; bs.leafDevice = g.leafDevice;
+    bs.nodes = g.nodes; bs.octNodes = g.octNodes; bs.leafShape = g.leafShape; bs.leafOrig = g.leafOrig; bs.leafDevice = g.leafDevice; bs.leafRecord = g.leafRecord;
     cudaComputeBvhReady = true;
     return VCRT_SUCCESS;
 }

@@ -54,6 +54,7 @@ struct BvhScene {
     const float4* leafShape;      // sorted order
     const uint32_t* leafOrig;
     const uint32_t* leafDevice;
+    const LeafRecord* leafRecord; // (shape, device index, original index) of a sorted leaf in one 32-byte sector
     const float4* shape;          // device order (exact tests of the always list, normals)
     const float4* surf;
     const int* kind;
@@ -212,7 +213,7 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
 #if LBVH_PREFETCH >= 1
                 if (far >= 0) asm volatile("prefetch.global.L1 [%0];" :: "l"(&nodes[first + (uint32_t)far]));
 #if LBVH_PREFETCH == 2
-                else asm volatile("prefetch.global.L1 [%0];" :: "l"(&scene.leafShape[~far]));
+                else asm volatile("prefetch.global.L1 [%0];" :: "l"(&scene.leafRecord[~far]));
 #endif
 #endif
                 continue;
@@ -221,7 +222,8 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
         } else {
             const int l = ~node;
             if (!VCRT_CHECK(n.counters, l >= 0 && (uint32_t)l < scene.treeCount)) break;
-            hit_ordered(__ldg(&scene.leafShape[l]), (int)__ldg(&scene.leafDevice[l]), __ldg(&scene.leafOrig[l]), ray, a, rec);
+            const uint2 ids = __ldg(reinterpret_cast<const uint2*>(&scene.leafRecord[l].device));
+            hit_ordered(__ldg(&scene.leafRecord[l].shape), (int)ids.x, ids.y, ray, a, rec);
             n.tests++;
         }
         if (sp == 0) break;

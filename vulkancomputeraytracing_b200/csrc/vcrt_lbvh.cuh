@@ -37,6 +37,8 @@ struct BvhNode {
 // (one base pointer) instead of with 12 selects per visit.  In the copies the two children are INTERLEAVED,
 //     a = (near0.x, near1.x, near0.y, near1.y)   b = (near0.z, near1.z, far0.x, far1.x)   c = (far0.y, far1.y, far0.z, far1.z)
 // so that one packed FFMA2 evaluates a slab plane of both children: 6 per visit instead of 12 FFMA.
+struct __align__(32) LeafRecord { float4 shape; uint32_t device, orig, pad0, pad1; };
+
 struct BvhBuildArgs {
     const float4* shape;        // device-order (cx, cy, cz, r)
     const uint32_t* origIndex;  // device index -> index in the caller's array
@@ -47,6 +49,7 @@ struct BvhBuildArgs {
     float4* leafShape;             // [count] sorted (cx, cy, cz, r)
     uint32_t* leafOrig;            // [count] sorted original index
     uint32_t* leafDevice;          // [count] sorted device index (surf / kind lookup)
+    struct LeafRecord* leafRecord; // [count] the three above in one 32-byte sector: what a leaf visit of the traversal loads
     BvhNode* nodes;                // [count-1]
     BvhNode* octNodes;             // [8][count-1], see above
     int* parent;                   // [2*count-1]: internal nodes 0..count-2, then leaves
@@ -84,6 +87,8 @@ __global__ void lbvh_leaves_kernel(BvhBuildArgs g) {
     g.leafShape[i] = s;
     g.leafOrig[i] = g.origIndex[j];
     g.leafDevice[i] = j;
+    LeafRecord rec; rec.shape = s; rec.device = j; rec.orig = g.origIndex[j]; rec.pad0 = rec.pad1 = 0u;
+    g.leafRecord[i] = rec;
     float r = fabsf(s.w);
     float* bb = g.bounds + 6 * (size_t)(g.count - 1 + i);
     bb[0] = __fsub_rd(s.x, r); bb[1] = __fsub_rd(s.y, r); bb[2] = __fsub_rd(s.z, r);

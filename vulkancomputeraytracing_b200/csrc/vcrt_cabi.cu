@@ -607,6 +607,14 @@ static int ensureBvh(void) {
         e.radiusMin = i ? fminf(e.radiusMin, r) : r; e.radiusMax = i ? fmaxf(e.radiusMax, r) : r;
     }
     bs.treeCount = n; bs.extraCount = extraCount;
+    if (extraCount > kMaxBvhExtras) return fail(VCRT_ERROR_UNSUPPORTED, "more spheres outside the tree than the constant table holds%s", "");
+    if (extraCount) {   // the records the traversal kernel reads from the constant bank (vcrt_kernel_lbvh.cuh)
+        LeafRecord records[kMaxBvhExtras]; memset(records, 0, sizeof records);
+        const uint32_t* hostOrig = (const uint32_t*)(cudaComputeHostBlob + hdr.offOrig);
+        for (uint32_t x = 0; x < extraCount; x++) { records[x].shape = cudaComputeHostShape[extraIndex[x]]; records[x].device = extraIndex[x]; records[x].orig = hostOrig[extraIndex[x]]; }
+        CUDA_TRY(cudaMemcpyToSymbolAsync(cLbvhExtras, records, sizeof(LeafRecord) * extraCount, 0, cudaMemcpyHostToDevice, cudaComputeStream));
+        CUDA_TRY(cudaStreamSynchronize(cudaComputeStream));   // `records` is on the stack
+    }
     bs.centreMin = make_float3(e.centreMin[0], e.centreMin[1], e.centreMin[2]); bs.centreMax = make_float3(e.centreMax[0], e.centreMax[1], e.centreMax[2]);
     bs.radiusMin = e.radiusMin; bs.radiusMax = e.radiusMax;
     bs.halfInvRadiusMin = nextafterf(0.5f / e.radiusMin, INFINITY);

@@ -78,6 +78,11 @@ struct BvhScene {
 #endif
 constexpr int lbvh_min_blocks(bool fixed, bool book) { return fixed && !book ? LBVH_BLOCKS : 4; }
 
+// The spheres outside the tree (outliers, then the always list; BvhScene::extra) as records in the constant bank: every ray tests
+// all of them, so the loads are warp-uniform - LDC / LDCU instead of an index load and two dependent global loads per sphere.
+constexpr uint32_t kMaxBvhExtras = 80u;   // 16 outliers + 64 always spheres (vcrt_cabi.cu)
+__constant__ LeafRecord cLbvhExtras[kMaxBvhExtras];
+
 struct OrderedHit { float t; int device; uint32_t orig; };
 
 // Candidate root of one sphere, independent of what was found before (see the file header).
@@ -140,7 +145,10 @@ VCRT_DEV void lbvh_nearest(const BvhScene& scene, const Ray& ray, float a, Order
         rec.t = h.t; rec.device = h.index;
         return;
     }
-    for (uint32_t x = 0; x < scene.extraCount; x++) { const uint32_t k = __ldg(&scene.extra[x]); hit_ordered(__ldg(&scene.shape[k]), (int)k, __ldg(&scene.origIndex[k]), ray, a, rec); n.tests++; }
+    for (uint32_t x = 0; x < scene.extraCount; x++) {
+        if (!VCRT_CHECK(n.counters, x < kMaxBvhExtras)) break;
+        hit_ordered(cLbvhExtras[x].shape, (int)cLbvhExtras[x].device, cLbvhExtras[x].orig, ray, a, rec); n.tests++;
+    }
     if (scene.treeCount == 1u) { hit_ordered(__ldg(&scene.leafShape[0]), (int)__ldg(&scene.leafDevice[0]), __ldg(&scene.leafOrig[0]), ray, a, rec); n.tests++; }
     if (scene.treeCount <= 1u) return;
     // per-ray widening of every box and the slab constants: as in render_lbvh_kernel

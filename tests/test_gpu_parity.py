@@ -437,6 +437,19 @@ def test_item_numbering_corner_cases(oracle, gpu_scene):
         assert sg.rays == cst["rays"] and np.abs(gpu - cpu).max() <= 2.0 ** -20
 
 
+@pytest.mark.parametrize("shape", [(65535, 1), (1, 65535), (16381, 5), (3, 20011), (8191, 9)])
+def test_extreme_aspect_ratios(oracle, gpu_scene, shape):
+    # the kernels turn tile and pixel indices into coordinates with reciprocal estimates instead of integer divisions
+    # (vcrt_device.cuh: udiv_small, tile_to_xy, pixel_to_xy): the widest and the tallest images the ABI accepts, odd sizes between
+    w, h = shape
+    cpu, cst = oracle.render(gpu_scene, w, h, 2, depth=4)
+    for trav in (BRUTE, LBVH):
+        gpu, sg = host.render(w, h, 2, depth=4, traversal=trav, sample_chunks=1)
+        assert_same(gpu, sg, cpu, cst)
+        fixed, sf = host.render(w, h, 2, depth=4, traversal=trav)          # brute force: primary pass + compact hand-over list
+        assert sf.rays == cst["rays"] and np.abs(fixed - cpu).max() <= 2.0 ** -22
+
+
 @pytest.mark.parametrize("traversal", [BRUTE, LBVH])
 def test_chunk_counts_that_do_not_divide_the_samples(oracle, gpu_scene, traversal):
     # 7 samples in 5 or 6 chunks are 4 runs of 2 (ceil(7 / ceil(7 / 5)) = 4), 9 samples in 4 chunks are 3 runs of 3: only the
